@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the trex_b200 hot path.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun)
+  python bench.py --impl reference ...                      (CPU port of the reference, rank 0)
+
+Metric (BASELINE.json): Sankoff fwd+bwd DP cell-updates/s, with the tree-cost grad steps/s of
+config c2 reported in the same JSON line under "tree_cost".
+
+Workload at every N: BASELINE config c5 — 1024 taxa x 100k sites, A=20, balanced tree, unit
+cost, synthetic edge-mutation alignment.  One step = one pass of the hot path over
+the rank's sites: device-built plan, hard forward (dp + argmins + score), traceback (+ edge
+histogram), relaxed forward, relaxed backward (marginals, leaf gradient, dC).  One DP
+cell-update = one dp[node, site, state] value of an internal node in one pass, so a step is
+4 * (n-1) * L * A cell-updates (SURVEY §8d unit definitions).  Sites are sharded over ranks
+(weak scaling by default: 100k sites per GPU; --scaling strong splits the 100k), and one packed
+NCCL all-reduce per step combines the scalar costs, dC and the edge histogram.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+  sys.path.insert(0, ROOT)
+
+N_LEAVES, N_STATES, N_SITES = 1024, 20, 100_000
+SOFT_T = 1.0
+METRIC = "sankoff_fwd_bwd_dp_cell_updates_per_s"
+UNIT = "cell-updates/s"
+
+
+def peaks():
+  p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+  if os.path.exists(p):
+    with open(p) as f:
+      return float(json.load(f)["hbm_gbs"]), "measured"
+  return 6650.0, "fallback"
+
+
+def alg_bytes_per_site(n, A):
+  """SURVEY §8(d) algorithmic (compulsory) bytes per site and tree, per pass."""
+  return {
+    "hard_fwd": n + (2 * n - 3) * 4 * A + (n - 1) * 2 * A,
+    "hard_bwd": 3 * (n - 1) + 1,
+    "soft_fwd": n + (2 * n - 3) * 4 * A,
+    "soft_bwd": n + (4 * n - 5) * 4 * A,
+  }
+
+
+def make_inputs(n, A, L, seed):
+  from trex_b200 import synth
+
+  rng = np.random.default_rng(seed)
+  par = synth.balanced_parents(n)
+  adj = synth.parents_to_adjacency(par)
+  states = synth.evolve(par, L, A, 0.1, rng)[:n]
+  return adj, synth.unit_cost(A), np.ascontiguousarray(states)
+
+
+class ClockSampler:
+  """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+  Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+       "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+  def __init__(self, index):
+    self.rows, self.proc, self.index = [], None, index
+
+  def start(self):
+    try:
+      self.proc = subprocess.Popen(
+        ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
+        stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+      threading.Thread(target=self._read, daemon=True).start()
+    except OSError:
+      self.proc = None
+
+  def _read(self):
+    for line in self.proc.stdout:
+      self.rows.append(line.strip())
+
+  def stop(self):
+    if self.proc is None:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    self.proc.terminate()
+    sm, mx, reasons = [], [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for r in self.rows:
+      f = [x.strip() for x in r.split(",")]
+      try:
+        sm.append(float(f[0]))
+        mx.append(float(f[1]))
+      except (ValueError, IndexError):
+        continue
+      for nm, val in zip(names, f[2:6]):
+        if val.lower().startswith("active"):
+          reasons.add(nm)
+    return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+            "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU arm: the plain-C port of the reference (oracle/), all host threads
+# ----------------------------------------------------------------------------------------------
+
+
+def cpu_step(adj, cost, seqs_f32, n, A):
+  from oracle import c_oracle
+
+  n_all = 2 * n - 1
+  c_oracle.run_sankoff(adj, cost, seqs_f32, n_all, A, n, return_path=True, want_dp=False)
+  c_oracle.soft_sankoff(adj, cost, seqs_f32, n_all, A, n, SOFT_T)
+
+
+def cpu_baseline(sample_sites):
+  from oracle import c_oracle
+
+  adj, cost, states = make_inputs(N_LEAVES, N_STATES, sample_sites, seed=5)
+  seqs = states.astype(np.float32)
+  cpu_step(adj, cost, seqs[:, :256].copy(), N_LEAVES, N_STATES)  # warm the thread pool
+  t0 = time.perf_counter()
+  cpu_step(adj, cost, seqs, N_LEAVES, N_STATES)
+  dt = time.perf_counter() - t0
+  cells = 4 * (N_LEAVES - 1) * sample_sites * N_STATES
+  return {"value": cells / dt, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port",
+          "sample": f"{sample_sites} of {N_SITES} sites of the c5 alignment, one pass (hard fwd+traceback, "
+                    f"relaxed fwd+bwd), plain-C OpenMP port of sankoff.py (JAX not installable)",
+          "seconds": dt}
+
+
+def run_reference(args):
+  rank = int(os.environ.get("RANK", "0"))
+  if rank != 0:
+    return
+  from oracle import c_oracle
+
+  sample = args.ref_sites
+  adj, cost, states = make_inputs(N_LEAVES, N_STATES, sample, seed=5)
+  seqs = states.astype(np.float32)
+  for _ in range(args.warmup):
+    cpu_step(adj, cost, seqs, N_LEAVES, N_STATES)
+  t0 = time.perf_counter()
+  for _ in range(args.steps):
+    cpu_step(adj, cost, seqs, N_LEAVES, N_STATES)
+  dt = time.perf_counter() - t0
+  cells = 4 * (N_LEAVES - 1) * sample * N_STATES * args.steps
+  val = cells / dt
+  desc = (f"{sample} of {N_SITES} sites per step; plain-C OpenMP port of the reference's sankoff.py "
+          f"(+ relaxed restatement); the reference itself is JAX, not installable offline")
+  line = {
+    "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+    "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+    "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
+    "data": "synthetic", "config": workload_config(args, sample),
+    "cpu_baseline": {"value": val, "unit": UNIT, "cores": c_oracle.num_threads(), "kind": "port", "sample": desc},
+    "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    "gpu_launches": 0,
+  }
+  print(json.dumps(line), flush=True)
+
+
+def workload_config(args, sites_per_rank):
+  return {"workload": "c5: 1024 taxa x 100k sites, A=20, balanced tree, unit cost; hard fwd + traceback + "
+                      "relaxed fwd + bwd (T=1), site-sharded",
+          "n_leaves": N_LEAVES, "n_states": N_STATES, "n_sites_total_c5": N_SITES,
+          "sites_per_rank": int(sites_per_rank), "parallelism": f"sites{args.gpus}",
+          "l2": "inputs_exceed_l2 (tables are GBs per pass; no explicit flush)"}
+
+
+# ----------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------
+
+
+def tree_cost_bench(torch, iters=200):
+  """BASELINE config c2: soft-topology tree_cost + grad, 64 taxa (127 nodes) x 1k sites, DNA."""
+  from oracle import tree_oracle as to
+  from trex_b200 import _lib
+  from trex_b200.tree import tree_cost_value_and_grad
+
+  rng = np.random.default_rng(2)
+  N, L, Q, n = 127, 1000, 4, 64
+  S = to.softmax(rng.normal(size=(N, L, Q))).astype(np.float32)
+  S[:n] = np.eye(Q, dtype=np.float32)[rng.integers(0, Q, size=(n, L))]
+  adj = to.update_tree(rng.normal(size=(N - 1, N - n)).astype(np.float32),
+                       np.zeros((N - 1, N - n), np.float32)).astype(np.float32)
+  St, At = torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda()
+  ws = torch.empty(_lib.load().trex_tree_cost_workspace_bytes(N, L * Q, Q), dtype=torch.uint8, device="cuda")
+  out = {"cost": torch.empty((), device="cuda"), "dS": torch.empty_like(St), "dA": torch.empty_like(At)}
+  for _ in range(10):
+    tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  torch.cuda.synchronize()
+  e0.record()
+  for _ in range(iters):
+    tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
+  e1.record()
+  torch.cuda.synchronize()
+  ms = e0.elapsed_time(e1) / iters
+  # CPU: NumPy (BLAS) restatement of the same value+grad, float32 like the reference
+  t0 = time.perf_counter()
+  reps = 5
+  for _ in range(reps):
+    to.soft_cost_value_and_grad(S, adj, None, dtype=np.float32)
+  cpu_ms = (time.perf_counter() - t0) / reps * 1e3
+  return {"metric": "tree_cost_grad_steps_per_s", "value": 1e3 / ms, "unit": "grad steps/s", "ms_per_step": ms,
+          "config": "c2: 127 nodes x 1000 sites x 4 states, identity cost, value + dS + dAdj",
+          "flop_per_step": 4 * N * N * L * Q, "bytes_per_step": 4 * N * L * Q * 2 + 8 * N * N,
+          "note": "launch/latency bound at this size (SURVEY H7)",
+          "cpu_baseline": {"value": 1e3 / cpu_ms, "unit": "grad steps/s", "kind": "port",
+                           "sample": "NumPy/BLAS float32 restatement of tree.py value+grad"}}
+
+
+def run_gpu(args):
+  import torch
+  import torch.distributed as dist
+
+  from trex_b200 import _lib
+  from trex_b200.sankoff import SankoffEngine
+
+  rank = int(os.environ.get("RANK", "0"))
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  if world != args.gpus:
+    if world == 1 and args.gpus > 1:
+      raise SystemExit("--gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+  torch.cuda.set_device(local)
+  if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+  _lib.load()
+
+  n, A = N_LEAVES, N_STATES
+  n_all = 2 * n - 1
+  L = args.sites if args.sites else (N_SITES if args.scaling == "weak" else (N_SITES + world - 1) // world)
+  adj_h, cost_h, states_h = make_inputs(n, A, L, seed=5 + rank)
+  # pinned host buffers: the e2e leg copies these every step
+  adj_p = torch.from_numpy(adj_h).pin_memory()
+  cost_p = torch.from_numpy(cost_h).pin_memory()
+  states_p = torch.from_numpy(states_h).pin_memory()
+  adj_d, cost_d, states_d = adj_p.cuda(), cost_p.cuda(), states_p.cuda()
+
+  eng = SankoffEngine(n_all, n, A, L)
+  from trex_b200.dist import PackedAllReduce
+  reducer = PackedAllReduce([(1,), (1,), (1, A, A), (1, A, A)], device="cuda")
+  packed_h = torch.empty(2 + 2 * A * A, dtype=torch.float64).pin_memory()
+  names = ["plan", "hard_fwd", "hard_bwd", "soft_fwd", "soft_bwd", "reduce"]
+  LAUNCHES_PER_STEP = 6  # plan (2 kernels), hard fwd, traceback, soft fwd, soft bwd
+
+  def step(ev=None):
+    def mark(i):
+      if ev is not None:
+        ev[i].record()
+    mark(0)
+    eng.set_adjacency(adj_d)
+    mark(1)
+    eng.hard_forward(cost_d, want_argmin=True)
+    mark(2)
+    eng.traceback(want_hist=True)
+    mark(3)
+    eng.soft_forward(cost_d, SOFT_T)
+    mark(4)
+    eng.soft_backward(cost_d, SOFT_T, want_dleaf=True, want_dcost=True)
+    mark(5)
+    # one packed all-reduce: [hard total, soft total, dC (A*A), edge histogram (A*A)]
+    reducer([eng.total, eng.soft_total, eng.dcost, eng.edge_hist])
+    mark(6)
+
+  eng.set_leaf_states_u8(states_d)
+  for _ in range(args.warmup):
+    step()
+  torch.cuda.synchronize()
+
+  def barrier():
+    if world > 1:
+      dist.barrier()
+    torch.cuda.synchronize()
+
+  # ---- timed region (device resident inputs) ------------------------------------------------
+  evs = [[torch.cuda.Event(enable_timing=True) for _ in range(7)] for _ in range(args.steps)]
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  sampler = ClockSampler(local)
+  if rank == 0:
+    sampler.start()
+  barrier()
+  e0.record()
+  for k in range(args.steps):
+    step(evs[k])
+  e1.record()
+  barrier()
+  ms_total = e0.elapsed_time(e1)
+  clocks = sampler.stop() if rank == 0 else None
+  kern_ms = {nm: float(np.mean([evs[k][i].elapsed_time(evs[k][i + 1]) for k in range(args.steps)]))
+             for i, nm in enumerate(names)}
+
+  # ---- end-to-end: host buffers in, host results out, through the public API ------------------
+  def e2e_step():
+    adj_x = adj_p.cuda(non_blocking=True)
+    cost_x = cost_p.cuda(non_blocking=True)
+    states_x = states_p.cuda(non_blocking=True)
+    eng.set_leaf_states_u8(states_x)
+    eng.set_adjacency(adj_x)
+    eng.hard_forward(cost_x, want_argmin=True)
+    eng.traceback(want_hist=True)
+    eng.soft_forward(cost_x, SOFT_T)
+    eng.soft_backward(cost_x, SOFT_T, want_dleaf=True, want_dcost=True)
+    reducer([eng.total, eng.soft_total, eng.dcost, eng.edge_hist])
+    packed_h.copy_(reducer.buf, non_blocking=True)
+
+  for _ in range(2):
+    e2e_step()
+  barrier()
+  f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  f0.record()
+  for _ in range(args.steps):
+    e2e_step()
+  f1.record()
+  barrier()
+  ms_e2e = f0.elapsed_time(f1)
+
+  t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device="cuda")
+  if world > 1:
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+  ms_total, ms_e2e = float(t[0]), float(t[1])
+  cells_step = 4 * (n - 1) * L * A * world
+  value = cells_step * args.steps / (ms_total * 1e-3)
+  e2e_value = cells_step * args.steps / (ms_e2e * 1e-3)
+
+  if rank == 0:
+    peak, peak_src = peaks()
+    per_site = alg_bytes_per_site(n, A)
+    roof_all = {}
+    for nm in ["hard_fwd", "hard_bwd", "soft_fwd", "soft_bwd"]:
+      gbs = per_site[nm] * L / (kern_ms[nm] * 1e-3) / 1e9
+      roof_all[nm] = {"ms": kern_ms[nm], "alg_bytes": per_site[nm] * L, "achieved": gbs, "frac": gbs / peak}
+    dom = max(["hard_fwd", "soft_fwd", "soft_bwd"], key=lambda k: kern_ms[k])
+    line = {
+      "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+      "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+      "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+      "config": workload_config(args, L),
+      "roofline": {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak,
+                   "peak_source": peak_src, "unit": "GB/s", "frac": roof_all[dom]["frac"], "traffic": None,
+                   "note": "achieved = SURVEY 8(d) algorithmic bytes / CUDA-event launch time on the launching stream"},
+      "roofline_all": roof_all,
+      "kernel_ms": kern_ms,
+      "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+              "h2d_bytes_per_step": int(states_p.numel() + adj_p.numel() * 4 + cost_p.numel() * 4),
+              "d2h_bytes_per_step": int(packed_h.numel() * 8)},
+      "gpu_launches": LAUNCHES_PER_STEP * args.steps,
+      "clocks": clocks,
+      "results": {"hard_total": float(packed_h[0]), "soft_total": float(packed_h[1])},
+    }
+    if world == 1 and not args.no_extras:
+      line["tree_cost"] = tree_cost_bench(torch)
+      line["cpu_baseline"] = cpu_baseline(args.cpu_sites)
+    print(json.dumps(line), flush=True)
+  if world > 1:
+    dist.destroy_process_group()
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument("--gpus", type=int, default=1)
+  ap.add_argument("--steps", type=int, default=10)
+  ap.add_argument("--warmup", type=int, default=3)
+  ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+  ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+  ap.add_argument("--sites", type=int, default=0, help="override sites per rank (testing)")
+  ap.add_argument("--cpu-sites", type=int, default=4096, help="sites of the bounded cpu_baseline sample")
+  ap.add_argument("--ref-sites", type=int, default=2048, help="sites per step of --impl reference")
+  ap.add_argument("--no-extras", action="store_true", help="skip tree_cost and cpu_baseline legs")
+  args = ap.parse_args()
+  args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+  if args.impl == "reference":
+    run_reference(args)
+  else:
+    run_gpu(args)
+
+
+if __name__ == "__main__":
+  main()

@@ -1,0 +1,157 @@
+/*
+ * trex_b200.h — C ABI of libtrex_b200.so: hand-written sm_100a CUDA kernels for the
+ * differentiable tree-scoring hot path of maraxen/trex.
+ *
+ * The reference has no native/FFI interface (it is pure Python/JAX): the boundary
+ * a maintainer binds is the Python signature of each jit-ed function.  Every entry point below
+ * names the reference function (file:line under /root/reference) whose body it replaces; the
+ * binding stubs (jax.ffi / ctypes) are shown in INTEGRATION.md.
+ *
+ * Conventions
+ *  - Plain pointers and sizes only.  All data pointers are DEVICE pointers unless the name ends
+ *    in `_host`.  Inputs are read-only; outputs and workspaces are caller-owned; the library
+ *    never allocates, frees or retains device memory and never synchronises the device.
+ *  - `stream` is a cudaStream_t passed as void*; all work is enqueued on it (graph-capturable).
+ *  - Return value: 0 = ok, non-zero = error; `trex_last_error()` returns a thread-local message.
+ *  - Native table layout is site-contiguous  [tree][node][state][site]  with row pitch
+ *    `site_stride` (elements, multiple of 16, >= n_sites).  Pad lanes are written with
+ *    unspecified values and are excluded from every reduction.
+ *  - Leaf states are uint8 codes: 0..A-1 observed state, >= A "no state" (the reference's
+ *    dropped out-of-bounds scatter, sankoff.py:50: the leaf row stays all-1e5).
+ *  - Internal node k (0-based) is node id n_leaves + k.  n_int = n_all - n_leaves.
+ */
+#ifndef TREX_B200_H_
+#define TREX_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define TREX_API __attribute__((visibility("default")))
+#else
+#define TREX_API
+#endif
+
+#define TREX_OK 0
+#define TREX_ERR_INVALID_ARGUMENT 1
+#define TREX_ERR_CUDA 2
+#define TREX_ERR_UNSUPPORTED 3
+
+/* inner-loop selection of the hard Sankoff forward (testing knob; AUTO is the product path) */
+#define TREX_MODE_AUTO 0    /* packed-key path when the cost matrix allows it, else exact-f32 */
+#define TREX_MODE_GENERAL 1 /* always the exact-f32 compare/select path */
+
+/* plan status bits (word 3 of each tree's plan header) */
+#define TREX_PLAN_HAS_SENTINEL_CHILD 1 /* some node has < 2 children, or a child id >= its own */
+#define TREX_PLAN_NOT_A_TREE 2         /* a node is the child of two parents; index order used */
+
+TREX_API const char* trex_last_error(void);
+TREX_API int trex_version(void);
+
+/* ---- tree schedule ------------------------------------------------------------------------
+ * Replaces the per-node `jnp.where(adj[:, node] == 1, size=2, fill_value=-1)` of
+ * src/trex/sankoff.py:60 and the fori_loop node order of :87-92 by a device-built plan:
+ * children of every internal node (first two rows equal to 1, ascending, -1 when missing)
+ * and a DFS post-order in which a child's row is consumed right after it is produced.
+ * `zero_root_selfloop` applies run_sankoff's `adj[-1,-1] = 0` (:141).  adj: [batch][n_all][n_all] f32.
+ * plan: [batch][trex_sankoff_plan_words()] int32. */
+TREX_API size_t trex_sankoff_plan_words(int n_all, int n_leaves);
+TREX_API int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
+                      int zero_root_selfloop, int32_t* plan, void* stream);
+
+/* ---- leaf encoding ------------------------------------------------------------------------
+ * `sequences[i].astype(int32)` + scatter index rules of src/trex/sankoff.py:49-52 (negative
+ * wraps, out-of-range dropped) applied once: f32 [n_leaves][in_stride] -> u8 [n_leaves][site_stride]. */
+TREX_API int trex_encode_leaf_states(const float* seqs, int n_leaves, int64_t n_sites, int64_t in_stride,
+                            int n_states, uint8_t* leaf_states, int64_t site_stride, void* stream);
+
+/* ---- hard Sankoff forward -----------------------------------------------------------------
+ * Replaces run_dp / vectorized_dp / the table part of run_sankoff
+ * (src/trex/sankoff.py:24-97, 141-160, 187).
+ *   leaf_states [n_leaves][site_stride] u8 (shared by all trees of the batch)
+ *   cost        [A][A] f32
+ *   dp          [batch][n_int][A][site_stride] f32 out (leaf rows are implicit)
+ *   argmin      [batch][n_int][2][A][site_stride] u8 out, or NULL (score/dp only)
+ *   root_min    [batch][site_stride] f32 out = min_s dp[root][s] per site, or NULL
+ *   total       [batch] f64 out = sum over sites of root_min, or NULL */
+TREX_API int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                          int64_t n_sites, int64_t site_stride, int batch,
+                          const uint8_t* leaf_states, const float* cost, float* dp,
+                          uint8_t* argmin, float* root_min, double* total, int mode,
+                          void* stream);
+
+/* ---- hard backward: ancestral-state traceback (+ optional edge histogram) ------------------
+ * Replaces the root argmin and backtrack_sankoff_jit (src/trex/sankoff.py:164-185, 191-267).
+ *   anc_states [batch][n_int][site_stride] u8 out (nodes unreachable from the root: 0)
+ *   edge_hist  [batch][A][A] u64 out or NULL: # of (parent state s, child state t) over all
+ *              edges and sites of the reconstruction = sub-gradient of the score w.r.t. cost. */
+TREX_API int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                           int64_t n_sites, int64_t site_stride, int batch,
+                           const uint8_t* leaf_states, const float* dp, const uint8_t* argmin,
+                           uint8_t* anc_states, unsigned long long* edge_hist, void* stream);
+
+/* ---- exports to the reference's layouts (what run_sankoff returns, sankoff.py:161-188) ------
+ *   dp_ref    [L][n_all][A] f32 incl. the explicit leaf rows (1e5 / 0)
+ *   recon_ref [n_all][L] f32: leaf rows = leaf_seqs_f32 (may be NULL -> decoded states),
+ *             ancestor rows = anc_states (or 0 when anc_states is NULL: return_path=False) */
+TREX_API int trex_sankoff_export_dp(int n_all, int n_leaves, int n_states, int64_t n_sites,
+                           int64_t site_stride, const uint8_t* leaf_states, const float* dp,
+                           float* dp_ref, void* stream);
+TREX_API int trex_sankoff_export_recon(int n_all, int n_leaves, int64_t n_sites, int64_t site_stride,
+                              const float* leaf_seqs_f32, int64_t leaf_in_stride,
+                              const uint8_t* leaf_states, const uint8_t* anc_states,
+                              float* recon_ref, void* stream);
+/* backtracking table of run_dp (sankoff.py:80-83): bt_ref [L][n_all][A][4] f32 */
+TREX_API int trex_sankoff_export_bt(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                           int64_t n_sites, int64_t site_stride, const uint8_t* argmin,
+                           float* bt_ref, void* stream);
+
+/* backtrack_sankoff_jit (sankoff.py:191-267) on the reference's own table layout:
+ *   bt_ref [n_sites][n_all][A][4] f32, root_node [1] i32, root_state [n_sites] i32
+ *   recon  [n_sites][n_all] i32 out (rows of leaves / unreached nodes are 0, as in the reference) */
+TREX_API int trex_sankoff_backtrack_ref(const float* bt_ref, int n_all, int n_leaves, int n_states,
+                               int64_t n_sites, const int32_t* root_node, const int32_t* root_state,
+                               int32_t* recon, void* stream);
+
+/* ---- relaxed (softmin) Sankoff forward / reverse (not in the reference) --
+ * min_t x -> -T*logsumexp_t(-x/T) in the recurrence of src/trex/sankoff.py:62-79 and :187.
+ * Leaves: either `leaf_states` (u8, hard leaves = 1e5*(1-onehot)) or `leaf_cost`
+ * [n_leaves][A][site_stride] f32 (soft leaves); exactly one is non-NULL.
+ *   dp     [batch][n_int][A][site_stride] f32 out
+ *   total  [batch] f64 out = sum over sites of softmin_s dp[root][s] */
+TREX_API int trex_sankoff_soft_fwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                          int64_t n_sites, int64_t site_stride, int batch,
+                          const uint8_t* leaf_states, const float* leaf_cost, const float* cost,
+                          float temperature, float* dp, double* total, void* stream);
+/*   gscale  device f32 scalar (upstream cotangent) or NULL = 1
+ *   gbar    [batch][n_int][A][site_stride] f32 out: d total / d dp[node] = soft ancestral marginals
+ *   dleaf   [batch][n_leaves][A][site_stride] f32 out or NULL: d total / d leaf_cost
+ *   dcost   [batch][A][A] f64 out or NULL */
+TREX_API int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                          int64_t n_sites, int64_t site_stride, int batch,
+                          const uint8_t* leaf_states, const float* leaf_cost, const float* cost,
+                          float temperature, const float* dp, const float* gscale, float* gbar,
+                          float* dleaf, double* dcost, void* stream);
+
+/* ---- soft-adjacency tree cost, value + gradients in one pass --------------------------------
+ * Replaces compute_surrogate_cost / compute_soft_cost (src/trex/tree.py:163-209, 212-266)
+ * and what jax.value_and_grad derives from them (src/trex/evals/benchmark.py:167-173).
+ *   seqs [N][K] f32, K = L*Q row-major (the reference's (N,L,Q) array, flat)
+ *   adj  [N][N] f32
+ *   cost NULL | [Q] (cost_kind 1) | [Q][Q] (cost_kind 2)
+ *   out_cost f32 scalar; d_seqs [N][K] or NULL; d_adj [N][N] or NULL; d_cost [Q]/[Q][Q] or NULL
+ *   workspace: trex_tree_cost_workspace_bytes(N, K, Q) bytes */
+TREX_API size_t trex_tree_cost_workspace_bytes(int n_nodes, int64_t k, int n_states);
+TREX_API int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cost, int cost_kind,
+                           int n_nodes, int64_t n_sites, int n_states, float* out_cost,
+                           float* d_seqs, float* d_adj, float* d_cost, void* workspace,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TREX_B200_H_ */

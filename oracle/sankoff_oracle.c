@@ -1,0 +1,216 @@
+/*
+ * TEST INFRASTRUCTURE ONLY — plain-C restatement of /root/reference/src/trex/sankoff.py, used
+ * (a) as a second checker beside the NumPy restatement and (b) as the timed CPU baseline of
+ * bench.py (`cpu_baseline`, `--impl reference`): the reference itself is JAX and JAX is not
+ * installable here, so this port stands in for it (kind = "port").  Never linked into, called
+ * from or shipped with trex_b200.
+ *
+ * It keeps the reference's data structures and control flow: per site a (n_all, A) f32 DP table
+ * filled with 1e5 (sankoff.py:152), a (n_all, A, 4) f32 back-pointer table (:151), index-order
+ * loop over internal nodes (:87-92), children = first two rows with adj[:, node] == 1 (:60,
+ * hoisted out of the site loop exactly as vmap hoists it), first-min argmin (:69), and the
+ * explicit-stack traceback (:212-265).  Sites are the vmap axis (:97) -> the OpenMP loop.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define SENTINEL 1e5f
+
+int oracle_num_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
+
+/* jnp.where(adj[:, node] == 1, size=2, fill_value=-1)[0] for every node (sankoff.py:60) */
+static void find_children(const float* adj, int n_all, int zero_root_selfloop, int* kids) {
+  for (int node = 0; node < n_all; ++node) {
+    int c = 0;
+    kids[2 * node] = kids[2 * node + 1] = -1;
+    for (int i = 0; i < n_all && c < 2; ++i) {
+      float v = adj[(size_t)i * n_all + node];
+      if (zero_root_selfloop && i == n_all - 1 && node == n_all - 1) v = 0.f; /* :141 */
+      if (v == 1.0f) kids[2 * node + c++] = i;
+    }
+  }
+}
+
+static inline int wrap(int idx, int n) { return idx < 0 ? idx + n : idx; }
+
+/* run_sankoff (sankoff.py:114-188).  seqs [n_rows][L] f32 (row pitch L); outputs in the
+ * reference's layouts: recon [n_all][L] f32, dp [L][n_all][A] f32 (may be NULL), root_min [L]
+ * (may be NULL), total f32.  Returns 0. */
+int oracle_run_sankoff(const float* adj, const float* cost, const float* seqs, int n_all, int A,
+                       int n_leaves, long L, int return_path, float* recon, float* dp_out,
+                       float* root_min, float* total) {
+  int* kids = (int*)malloc(sizeof(int) * 2 * (size_t)n_all);
+  find_children(adj, n_all, 1, kids);
+  const int dp_leaves = (n_all + 1) / 2; /* run_dp derives it from the shape, :45-46 */
+  double tot = 0.0;
+#pragma omp parallel reduction(+ : tot)
+  {
+    float* dp = (float*)malloc(sizeof(float) * (size_t)n_all * A);
+    float* bt = (float*)malloc(sizeof(float) * (size_t)n_all * A * 4);
+    int* stack = (int*)malloc(sizeof(int) * 2 * ((size_t)n_all + 2));
+    int* rec = (int*)malloc(sizeof(int) * (size_t)n_all);
+#pragma omp for schedule(static)
+    for (long l = 0; l < L; ++l) {
+      for (int i = 0; i < n_all * A; ++i) dp[i] = SENTINEL;
+      memset(bt, 0, sizeof(float) * (size_t)n_all * A * 4);
+      for (int i = 0; i < dp_leaves; ++i) { /* :49-52 */
+        int s = (int)seqs[(size_t)i * L + l];
+        if (s < 0) s += A;
+        if (s >= 0 && s < A) dp[i * A + s] = 0.f;
+      }
+      for (int node = dp_leaves; node < n_all; ++node) { /* :87-92 */
+        float* out = dp + (size_t)node * A;
+        float acc[64];
+        for (int s = 0; s < A; ++s) acc[s] = 0.f;
+        for (int k = 0; k < 2; ++k) { /* scan over the two children, :73-77 */
+          const int child = wrap(kids[2 * node + k], n_all);
+          const float* d = dp + (size_t)child * A;
+          for (int s = 0; s < A; ++s) {
+            const float* c = cost + (size_t)s * A;
+            float best = c[0] + d[0];
+            int bi = 0;
+            for (int t = 1; t < A; ++t) {
+              const float x = c[t] + d[t];
+              if (x < best) { best = x; bi = t; }
+            }
+            acc[s] += best;
+            bt[((size_t)node * A + s) * 4 + 2 * k] = (float)kids[2 * node + k];
+            bt[((size_t)node * A + s) * 4 + 2 * k + 1] = (float)bi;
+          }
+        }
+        for (int s = 0; s < A; ++s) out[s] = acc[s]; /* :79 */
+      }
+      /* score: dp[:, -1].min(axis=1) summed over sites, :187 */
+      const float* root = dp + (size_t)(n_all - 1) * A;
+      float rm = root[0];
+      int rs = 0;
+      for (int s = 1; s < A; ++s)
+        if (root[s] < rm) { rm = root[s]; rs = s; }
+      tot += (double)rm;
+      if (root_min) root_min[l] = rm;
+      if (dp_out) memcpy(dp_out + (size_t)l * n_all * A, dp, sizeof(float) * (size_t)n_all * A);
+      for (int i = 0; i < n_all; ++i)
+        recon[(size_t)i * L + l] = i < n_leaves ? seqs[(size_t)i * L + l] : 0.f; /* :161-162 */
+      if (return_path) { /* :164-185, 212-265 */
+        for (int i = 0; i < n_all; ++i) rec[i] = 0;
+        int ptr = 1;
+        stack[0] = n_all - 1;
+        stack[1] = rs;
+        while (ptr > 0) {
+          --ptr;
+          const int node = stack[2 * ptr], state = stack[2 * ptr + 1];
+          if (node >= n_leaves) {
+            rec[node] = state;
+            const float* info = bt + ((size_t)node * A + state) * 4;
+            stack[2 * ptr] = (int)info[0];
+            stack[2 * ptr + 1] = (int)info[1];
+            stack[2 * ptr + 2] = (int)info[2];
+            stack[2 * ptr + 3] = (int)info[3];
+            ptr += 2;
+          }
+        }
+        for (int i = n_leaves; i < n_all; ++i) recon[(size_t)i * L + l] = (float)rec[i];
+      }
+    }
+    free(dp); free(bt); free(stack); free(rec);
+  }
+  *total = (float)tot;
+  free(kids);
+  return 0;
+}
+
+/* Relaxed forward + reverse (not in the reference — restatement of :55-92 with
+ * min -> -T*logsumexp(-x/T), float32 like the reference's default dtype).  Hard leaves.
+ * gbar_root_only: outputs are the total, dC [A][A] f64 and (optionally) the marginals
+ * gbar [L][n_all][A] f32. */
+int oracle_soft_sankoff(const float* adj, const float* cost, const float* seqs, int n_all, int A,
+                        int n_leaves, long L, float T, double* total, double* dC, float* gbar_out) {
+  int* kids = (int*)malloc(sizeof(int) * 2 * (size_t)n_all);
+  find_children(adj, n_all, 1, kids);
+  double tot = 0.0;
+  for (int i = 0; i < A * A; ++i) dC[i] = 0.0;
+#pragma omp parallel reduction(+ : tot)
+  {
+    float* dp = (float*)malloc(sizeof(float) * (size_t)n_all * A);
+    float* g = (float*)malloc(sizeof(float) * (size_t)n_all * A);
+    double* dcl = (double*)calloc((size_t)A * A, sizeof(double));
+    float w[64];
+#pragma omp for schedule(static)
+    for (long l = 0; l < L; ++l) {
+      for (int i = 0; i < n_all * A; ++i) dp[i] = SENTINEL;
+      for (int i = 0; i < n_leaves; ++i) {
+        int s = (int)seqs[(size_t)i * L + l];
+        if (s < 0) s += A;
+        if (s >= 0 && s < A) dp[i * A + s] = 0.f;
+      }
+      for (int node = n_leaves; node < n_all; ++node) {
+        for (int s = 0; s < A; ++s) {
+          float acc = 0.f;
+          for (int k = 0; k < 2; ++k) {
+            const int child = wrap(kids[2 * node + k], n_all);
+            const int valid = child < node;
+            const float* c = cost + (size_t)s * A;
+            float m = INFINITY;
+            for (int t = 0; t < A; ++t) {
+              w[t] = c[t] + (valid ? dp[(size_t)child * A + t] : SENTINEL);
+              if (w[t] < m) m = w[t];
+            }
+            float z = 0.f;
+            for (int t = 0; t < A; ++t) z += expf(-(w[t] - m) / T);
+            acc += m - T * logf(z);
+          }
+          dp[(size_t)node * A + s] = acc;
+        }
+      }
+      const float* root = dp + (size_t)(n_all - 1) * A;
+      float m = root[0];
+      for (int s = 1; s < A; ++s) if (root[s] < m) m = root[s];
+      float z = 0.f;
+      for (int s = 0; s < A; ++s) z += expf(-(root[s] - m) / T);
+      tot += (double)(m - T * logf(z));
+      memset(g, 0, sizeof(float) * (size_t)n_all * A);
+      for (int s = 0; s < A; ++s) g[(size_t)(n_all - 1) * A + s] = expf(-(root[s] - m) / T) / z;
+      for (int node = n_all - 1; node >= n_leaves; --node) {
+        for (int k = 0; k < 2; ++k) {
+          const int child = wrap(kids[2 * node + k], n_all);
+          const int valid = child < node;
+          for (int s = 0; s < A; ++s) {
+            const float gs = g[(size_t)node * A + s];
+            if (gs == 0.f) continue;
+            const float* c = cost + (size_t)s * A;
+            float mm = INFINITY;
+            for (int t = 0; t < A; ++t) {
+              w[t] = c[t] + (valid ? dp[(size_t)child * A + t] : SENTINEL);
+              if (w[t] < mm) mm = w[t];
+            }
+            float zz = 0.f;
+            for (int t = 0; t < A; ++t) { w[t] = expf(-(w[t] - mm) / T); zz += w[t]; }
+            for (int t = 0; t < A; ++t) {
+              const float contrib = gs * w[t] / zz;
+              dcl[(size_t)s * A + t] += (double)contrib;
+              if (valid) g[(size_t)child * A + t] += contrib;
+            }
+          }
+        }
+      }
+      if (gbar_out) memcpy(gbar_out + (size_t)l * n_all * A, g, sizeof(float) * (size_t)n_all * A);
+    }
+#pragma omp critical
+    for (int i = 0; i < A * A; ++i) dC[i] += dcl[i];
+    free(dp); free(g); free(dcl);
+  }
+  *total = tot;
+  free(kids);
+  return 0;
+}

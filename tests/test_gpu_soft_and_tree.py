@@ -1,0 +1,158 @@
+"""GPU parity tests: relaxed (softmin) Sankoff forward/backward and the soft-adjacency tree cost,
+through the C ABI, against the float64 oracle.  Tolerance: 1e-5 relative (BASELINE north star),
+written out in each assertion."""
+
+import numpy as np
+import pytest
+
+from oracle import sankoff_oracle as so
+from oracle import tree_oracle as to
+from trex_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5
+
+
+def _relerr(got, want):
+  got, want = np.asarray(got, dtype=np.float64), np.asarray(want, dtype=np.float64)
+  return np.abs(got - want).max() / max(np.abs(want).max(), 1e-30)
+
+
+def _soft_case(kind, n, A, L, seed, cost_kind):
+  rng = np.random.default_rng(seed)
+  par = synth.balanced_parents(n) if kind == "balanced" else (
+    synth.caterpillar_parents(n) if kind == "cat" else synth.random_join_parents(n, rng))
+  adj = synth.parents_to_adjacency(par)
+  states = synth.evolve(par, L, A, 0.2, rng)
+  cost = synth.unit_cost(A) if cost_kind == "unit" else (
+    synth.random_int_cost(A, 5, rng) if cost_kind == "int" else (rng.random((A, A)) * 2).astype(np.float32))
+  return adj, cost, states
+
+
+SOFT_CASES = [
+  ("balanced", 16, 4, 100, "unit", 1.0),
+  ("random", 11, 20, 37, "int", 1.0),
+  ("random", 11, 20, 37, "int", 0.1),
+  ("cat", 9, 5, 20, "float", 0.5),
+  ("random", 14, 2, 300, "unit", 0.3),
+  ("random", 8, 4, 50, "int", 0.01),   # max(C)/T > 80 -> direct (non exp-domain) evaluation
+  ("random", 6, 24, 21, "unit", 0.7),  # padded AP=32 kernels
+]
+
+
+@pytest.mark.parametrize("kind,n,A,L,ck,T", SOFT_CASES)
+def test_soft_forward_backward_hard_leaves(kind, n, A, L, ck, T):
+  import torch
+  from trex_b200.sankoff import SankoffEngine
+
+  adj, cost, states = _soft_case(kind, n, A, L, seed=n * 17 + A + L, cost_kind=ck)
+  n_all = 2 * n - 1
+  lc = so.leaf_cost_from_states(states[:n], A)
+  dp64, tot64 = so.soft_sankoff_fwd(adj, cost, lc, n_all, n, T)
+  g64, dC64 = so.soft_sankoff_bwd(adj, cost, dp64, n_all, n, T)
+  eng = SankoffEngine(n_all, n, A, L)
+  eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states[:n]))
+  eng.soft_forward(torch.from_numpy(cost), T)
+  dp = eng.export_dp(soft=True).cpu().numpy()
+  assert _relerr(dp[:, n:], dp64[:, n:]) <= RTOL
+  assert abs(float(eng.soft_total[0]) - tot64) <= RTOL * abs(tot64)
+  eng.soft_backward(torch.from_numpy(cost), T)
+  gbar = eng.gbar[0, :, :, :L].permute(2, 0, 1).cpu().numpy()  # (L, n_int, A)
+  assert np.abs(gbar - g64[:, n:]).max() <= RTOL  # marginals are O(1) probabilities
+  dleaf = eng.dleaf[0, :, :, :L].permute(2, 0, 1).cpu().numpy()
+  assert np.abs(dleaf - g64[:, :n]).max() <= RTOL
+  assert _relerr(eng.dcost[0].cpu().numpy(), dC64) <= RTOL
+
+
+def test_soft_leaves_and_autograd_scaling():
+  import torch
+  from trex_b200.relaxed import soft_sankoff_cost, to_native_leaf_cost
+  from trex_b200.sankoff import SankoffEngine
+
+  rng = np.random.default_rng(9)
+  n, A, L, T = 10, 4, 45, 0.8
+  adj, cost, _ = _soft_case("random", n, A, L, seed=5, cost_kind="int")
+  n_all = 2 * n - 1
+  lc = rng.random((n, L, A)) * 3
+  dp64, tot64 = so.soft_sankoff_fwd(adj, cost, lc, n_all, n, T)
+  g64, dC64 = so.soft_sankoff_bwd(adj, cost, dp64, n_all, n, T, g=2.5)
+  eng = SankoffEngine(n_all, n, A, L)
+  C = torch.from_numpy(cost).cuda().requires_grad_(True)
+  leaf = to_native_leaf_cost(torch.from_numpy(lc.astype(np.float32)).cuda()).requires_grad_(True)
+  total = soft_sankoff_cost(torch.from_numpy(adj), C, leaf, n_all, A, n, T, engine=eng)
+  assert abs(float(total) - tot64) <= RTOL * abs(tot64)
+  (2.5 * total).backward()
+  assert _relerr(C.grad.cpu().numpy(), dC64) <= RTOL
+  dleaf = leaf.grad[:, :, :L].permute(2, 0, 1).cpu().numpy()
+  assert np.abs(dleaf - g64[:, :n]).max() <= 2.5 * RTOL
+
+
+def test_soft_limit_T_to_zero_is_hard_score():
+  import torch
+  from trex_b200.sankoff import SankoffEngine
+
+  adj, cost, states = _soft_case("balanced", 32, 4, 500, seed=2, cost_kind="unit")
+  eng = SankoffEngine(63, 32, 4, 500)
+  eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states[:32]))
+  hard = float(eng.hard_forward(torch.from_numpy(cost))[0])
+  soft = float(eng.soft_forward(torch.from_numpy(cost), 0.02)[0])
+  assert hard - 0.05 * 500 <= soft <= hard + 1e-3
+
+
+def _tree_inputs(N, L, Q, seed, adj_kind):
+  rng = np.random.default_rng(seed)
+  n = (N + 1) // 2
+  S = to.softmax(rng.normal(size=(N, L, Q))).astype(np.float32)
+  S[:n] = np.eye(Q, dtype=np.float32)[rng.integers(0, Q, size=(n, L))]  # one-hot leaves
+  if adj_kind == "bernoulli":  # benchmark_tree_cost.py:57
+    adj = (rng.random((N, N)) < 0.1).astype(np.float32)
+  else:  # row-softmax over the update_tree mask structure (tree.py:81-107)
+    adj = to.update_tree(rng.normal(size=(N - 1, N - n)).astype(np.float32),
+                         np.zeros((N - 1, N - n), np.float32)).astype(np.float32)
+  return S, adj, rng
+
+
+TREE_CASES = [(127, 1000, 4, "softmax"), (127, 1000, 4, "bernoulli"), (10, 100, 20, "bernoulli"),
+              (50, 200, 20, "bernoulli"), (200, 150, 20, "bernoulli"), (7, 3, 5, "softmax"), (65, 33, 3, "softmax")]
+
+
+@pytest.mark.parametrize("N,L,Q,ak", TREE_CASES)
+@pytest.mark.parametrize("ckind", ["none", "unit", "vector", "asym"])
+def test_tree_cost_value_and_grads(N, L, Q, ak, ckind):
+  import torch
+  from trex_b200.tree import tree_cost_value_and_grad
+
+  S, adj, rng = _tree_inputs(N, L, Q, seed=N + L + Q, adj_kind=ak)
+  C = {"none": None, "unit": synth.unit_cost(Q), "vector": (rng.random(Q) + 0.5).astype(np.float32),
+       "asym": rng.random((Q, Q)).astype(np.float32)}[ckind]
+  want, dS64, dA64, dC64 = to.soft_cost_value_and_grad(S, adj, C)
+  _, (t1, t2, t3) = to.compute_soft_cost(S, adj, C, dtype=np.float64)
+  cost, dS, dA, dC = tree_cost_value_and_grad(
+    torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda(), None if C is None else torch.from_numpy(C).cuda())
+  # the expanded quadratic form cancels; bound = 1e-5 relative + 4 eps32 of the terms
+  bound = RTOL * abs(want) + 4 * np.finfo(np.float32).eps * (abs(t1) + abs(t2) + abs(t3))
+  assert abs(float(cost) - want) <= bound
+  assert _relerr(dS.cpu().numpy(), dS64) <= RTOL
+  assert _relerr(dA.cpu().numpy(), dA64) <= RTOL
+  if C is not None:
+    assert _relerr(dC.cpu().numpy(), dC64) <= RTOL
+  naive = to.naive_compute_soft_cost(S, adj, C)
+  assert abs(float(cost) - naive) <= bound + 1e-9 * abs(naive)
+
+
+def test_tree_cost_autograd_matches_reference_signatures():
+  import torch
+  from trex_b200.tree import compute_soft_cost, compute_surrogate_cost
+
+  S, adj, _ = _tree_inputs(15, 20, 4, seed=1, adj_kind="softmax")
+  St = torch.from_numpy(S).cuda().requires_grad_(True)
+  At = torch.from_numpy(adj).cuda().requires_grad_(True)
+  c = compute_surrogate_cost(St, At)
+  assert c.shape == () and float(c) >= 0  # tests/test_tree.py:54-61
+  (3.0 * c).backward()
+  want, dS64, dA64, _ = to.soft_cost_value_and_grad(S, adj, None)
+  assert _relerr(St.grad.cpu().numpy(), 3.0 * dS64) <= RTOL
+  assert _relerr(At.grad.cpu().numpy(), 3.0 * dA64) <= RTOL
+  c2 = compute_soft_cost(St.detach(), At.detach(), torch.eye(4, device="cuda"))
+  assert abs(float(c2) - float(c)) <= RTOL * abs(float(c))

@@ -1,0 +1,157 @@
+// Shared helpers for the libtrex_b200 kernels (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/trex_b200.h"
+
+namespace trex {
+
+constexpr float kSentinel = 1e5f;  // src/trex/sankoff.py:152
+constexpr int kPlanHdr = 8;        // int32 header words per tree plan
+
+// plan word offsets (per tree); n_int = n_all - n_leaves
+struct PlanView {
+  const int32_t* base;
+  int n_int;
+  __host__ __device__ PlanView(const int32_t* b, int n) : base(b), n_int(n) {}
+  __device__ const int32_t* hdr() const { return base; }
+  __device__ const int32_t* child(int k) const { return base + kPlanHdr + k * n_int; }      // k=0,1
+  __device__ const int32_t* raw(int k) const { return base + kPlanHdr + (2 + k) * n_int; }  // k=0,1
+  __device__ const int32_t* order() const { return base + kPlanHdr + 4 * n_int; }
+};
+
+void set_error(const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+int sm_count();
+
+#define TREX_CHECK_ARG(cond, ...)        \
+  do {                                   \
+    if (!(cond)) {                       \
+      ::trex::set_error(__VA_ARGS__);    \
+      return TREX_ERR_INVALID_ARGUMENT;  \
+    }                                    \
+  } while (0)
+
+#define TREX_CHECK_LAUNCH(what)                                                 \
+  do {                                                                          \
+    int _rc = ::trex::check_cuda(cudaPeekAtLastError(), what);                  \
+    if (_rc) return _rc;                                                        \
+  } while (0)
+
+// ---- vector load/store of V consecutive sites --------------------------------------------
+template <int V> struct VecF;
+template <> struct VecF<1> { using type = float; };
+template <> struct VecF<2> { using type = float2; };
+template <> struct VecF<4> { using type = float4; };
+
+template <int V>
+__device__ __forceinline__ void ld_f(const float* __restrict__ p, float (&out)[V]) {
+  if constexpr (V == 1) {
+    out[0] = *p;
+  } else if constexpr (V == 2) {
+    float2 t = *reinterpret_cast<const float2*>(p);
+    out[0] = t.x; out[1] = t.y;
+  } else {
+    float4 t = *reinterpret_cast<const float4*>(p);
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+  }
+}
+
+// streaming read of data that is not re-read by this kernel (evict-first, bypass L1)
+template <int V>
+__device__ __forceinline__ void ld_f_stream(const float* __restrict__ p, float (&out)[V]) {
+  if constexpr (V == 1) {
+    out[0] = __ldcs(p);
+  } else if constexpr (V == 2) {
+    float2 t = __ldcs(reinterpret_cast<const float2*>(p));
+    out[0] = t.x; out[1] = t.y;
+  } else {
+    float4 t = __ldcs(reinterpret_cast<const float4*>(p));
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+  }
+}
+
+template <int V>
+__device__ __forceinline__ void st_f(float* __restrict__ p, const float (&v)[V]) {
+  if constexpr (V == 1) {
+    *p = v[0];
+  } else if constexpr (V == 2) {
+    *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+  } else {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+}
+
+// write-once outputs that this kernel never reads back (streaming store)
+template <int V>
+__device__ __forceinline__ void st_f_stream(float* __restrict__ p, const float (&v)[V]) {
+  if constexpr (V == 1) {
+    __stcs(p, v[0]);
+  } else if constexpr (V == 2) {
+    __stcs(reinterpret_cast<float2*>(p), make_float2(v[0], v[1]));
+  } else {
+    __stcs(reinterpret_cast<float4*>(p), make_float4(v[0], v[1], v[2], v[3]));
+  }
+}
+
+template <int V>
+__device__ __forceinline__ void ld_u8(const uint8_t* __restrict__ p, int (&out)[V]) {
+  if constexpr (V == 1) {
+    out[0] = *p;
+  } else if constexpr (V == 2) {
+    uchar2 t = *reinterpret_cast<const uchar2*>(p);
+    out[0] = t.x; out[1] = t.y;
+  } else {
+    uchar4 t = *reinterpret_cast<const uchar4*>(p);
+    out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
+  }
+}
+
+template <int V>
+__device__ __forceinline__ void st_u8(uint8_t* __restrict__ p, const int (&v)[V]) {
+  if constexpr (V == 1) {
+    *p = (uint8_t)v[0];
+  } else if constexpr (V == 2) {
+    *reinterpret_cast<uchar2*>(p) = make_uchar2((uint8_t)v[0], (uint8_t)v[1]);
+  } else {
+    *reinterpret_cast<uchar4*>(p) =
+        make_uchar4((uint8_t)v[0], (uint8_t)v[1], (uint8_t)v[2], (uint8_t)v[3]);
+  }
+}
+
+template <int V>
+__device__ __forceinline__ void st_u8_stream(uint8_t* __restrict__ p, const int (&v)[V]) {
+  if constexpr (V == 1) {
+    __stcs(p, (uint8_t)v[0]);
+  } else if constexpr (V == 2) {
+    __stcs(reinterpret_cast<uchar2*>(p), make_uchar2((uint8_t)v[0], (uint8_t)v[1]));
+  } else {
+    __stcs(reinterpret_cast<uchar4*>(p),
+           make_uchar4((uint8_t)v[0], (uint8_t)v[1], (uint8_t)v[2], (uint8_t)v[3]));
+  }
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// block-wide sum of doubles -> one atomicAdd per block (blockDim.x multiple of 32, <= 1024)
+__device__ __forceinline__ void block_atomic_add(double v, double* dst) {
+  __shared__ double red[32];
+  v = warp_sum(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    v = lane < nw ? red[lane] : 0.0;
+    v = warp_sum(v);
+    if (lane == 0) atomicAdd(dst, v);
+  }
+}
+
+}  // namespace trex

@@ -1,0 +1,304 @@
+// Hard-Sankoff companions: leaf encoding, ancestral-state traceback (+ edge histogram) and
+// the exports from the native site-contiguous tables to the reference's array layouts.
+#include "common.cuh"
+
+namespace trex {
+
+// ---- leaf encoding: sequences[i].astype(int32) + scatter index rules (sankoff.py:49-52) ----
+__global__ void encode_leaf_kernel(const float* __restrict__ seqs, int n_leaves, long long n_sites,
+                                   long long in_stride, int A, uint8_t* __restrict__ out,
+                                   long long stride) {
+  const long long l = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.y;
+  if (l >= stride) return;
+  int code = 255;
+  if (l < n_sites) {
+    int s = (int)seqs[(size_t)i * in_stride + l];  // f32 -> int32 truncates toward zero
+    if (s < 0) s += A;                             // negative indices wrap
+    if (s >= 0 && s < A) code = s;                 // out-of-bounds updates are dropped
+  }
+  out[(size_t)i * stride + l] = (uint8_t)code;
+}
+
+// ---- traceback -----------------------------------------------------------------------------
+// Top-down pointer chase over the reverse post-order of the root's subtree; equivalent to the
+// explicit-stack DFS of backtrack_sankoff_jit (sankoff.py:212-265) on a tree.
+struct TraceParams {
+  const int32_t* plan;
+  size_t plan_words;
+  int n_all, n_leaves, n_states;
+  long long n_sites, stride;
+  const uint8_t* leaf;
+  const float* dp;
+  const uint8_t* arg;
+  uint8_t* anc;
+  unsigned long long* hist;
+};
+
+template <int V, int THREADS>
+__global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p) {
+  extern __shared__ unsigned int s_hist[];  // [A*A] when p.hist
+  const int A = p.n_states;
+  const int tree = blockIdx.y;
+  const int n_int = p.n_all - p.n_leaves;
+  PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+  if (p.hist) {
+    for (int i = threadIdx.x; i < A * A; i += THREADS) s_hist[i] = 0;
+    __syncthreads();
+  }
+  const long long site0 = ((long long)blockIdx.x * THREADS + threadIdx.x) * V;
+  if (site0 < p.n_sites) {
+    const float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
+    const uint8_t* arg = p.arg + (size_t)tree * n_int * 2 * A * p.stride + site0;
+    uint8_t* anc = p.anc + (size_t)tree * n_int * p.stride + site0;
+    const uint8_t* leaf = p.leaf + site0;
+    const int32_t* order = plan.order();
+    const int n_reach = plan.hdr()[1];
+    // nodes the root does not reach keep the reference's zero initialisation (sankoff.py:215)
+    int zero[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) zero[v] = 0;
+    for (int i = n_reach; i < n_int; ++i)
+      st_u8<V>(anc + (size_t)(__ldg(order + i) - p.n_leaves) * p.stride, zero);
+    // root state: first argmin of the root row (sankoff.py:172)
+    {
+      const int k = n_int - 1;
+      float best[V];
+      int st[V];
+      ld_f<V>(dp + (size_t)k * A * p.stride, best);
+#pragma unroll
+      for (int v = 0; v < V; ++v) st[v] = 0;
+      for (int s = 1; s < A; ++s) {
+        float x[V];
+        ld_f<V>(dp + ((size_t)k * A + s) * p.stride, x);
+#pragma unroll
+        for (int v = 0; v < V; ++v)
+          if (x[v] < best[v]) { best[v] = x[v]; st[v] = s; }
+      }
+      st_u8<V>(anc + (size_t)k * p.stride, st);
+    }
+    for (int i = n_reach - 1; i >= 0; --i) {
+      const int node = __ldg(order + i);
+      const int k = node - p.n_leaves;
+      int st[V];
+      ld_u8<V>(anc + (size_t)k * p.stride, st);
+#pragma unroll
+      for (int v = 0; v < V; ++v) st[v] = min(st[v], A - 1);  // pad lanes may hold anything
+#pragma unroll
+      for (int slot = 0; slot < 2; ++slot) {
+        const int c = __ldg(plan.child(slot) + k);
+        int cs[V];
+        if (c >= p.n_leaves) {
+#pragma unroll
+          for (int v = 0; v < V; ++v)
+            cs[v] = __ldcs(arg + (((size_t)k * 2 + slot) * A + st[v]) * p.stride + v);
+          st_u8<V>(anc + (size_t)(c - p.n_leaves) * p.stride, cs);
+        } else if (c >= 0 && p.hist) {
+          ld_u8<V>(leaf + (size_t)c * p.stride, cs);
+        }
+        if (p.hist && c >= 0) {
+#pragma unroll
+          for (int v = 0; v < V; ++v)
+            if (site0 + v < p.n_sites && cs[v] < A) atomicAdd(&s_hist[st[v] * A + cs[v]], 1u);
+        }
+      }
+    }
+  }
+  if (p.hist) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < A * A; i += THREADS)
+      if (s_hist[i]) atomicAdd(p.hist + (size_t)tree * A * A + i, (unsigned long long)s_hist[i]);
+  }
+}
+
+// ---- exports -------------------------------------------------------------------------------
+// dp_ref[l][node][s] from dp[k][s][l]: 32x32 shared-memory transpose, both sides coalesced.
+__global__ void __launch_bounds__(256)
+    export_dp_kernel(int n_all, int n_leaves, int A, long long n_sites, long long stride,
+                     const uint8_t* __restrict__ leaf, const float* __restrict__ dp,
+                     float* __restrict__ out) {
+  __shared__ float tile[32][33];
+  const long long J = (long long)n_all * A;
+  const long long l0 = (long long)blockIdx.x * 32, j0 = (long long)blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const long long j = j0 + r, l = l0 + threadIdx.x;
+    float v = 0.f;
+    if (j < J && l < n_sites) {
+      const int node = (int)(j / A), s = (int)(j % A);
+      if (node < n_leaves) v = (leaf[(size_t)node * stride + l] == s) ? 0.f : kSentinel;
+      else v = dp[((size_t)(node - n_leaves) * A + s) * stride + l];
+    }
+    tile[r][threadIdx.x] = v;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += 8) {
+    const long long l = l0 + r, j = j0 + threadIdx.x;
+    if (l < n_sites && j < J) out[(size_t)l * J + j] = tile[threadIdx.x][r];
+  }
+}
+
+__global__ void export_recon_kernel(int n_all, int n_leaves, long long n_sites, long long stride,
+                                    const float* __restrict__ leaf_f32, long long leaf_in_stride,
+                                    const uint8_t* __restrict__ leaf, const uint8_t* __restrict__ anc,
+                                    float* __restrict__ out) {
+  const long long l = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int node = blockIdx.y;
+  if (l >= n_sites) return;
+  float v = 0.f;
+  if (node < n_leaves) {
+    v = leaf_f32 ? leaf_f32[(size_t)node * leaf_in_stride + l] : (float)leaf[(size_t)node * stride + l];
+  } else if (anc) {
+    v = (float)anc[(size_t)(node - n_leaves) * stride + l];
+  }
+  out[(size_t)node * n_sites + l] = v;
+}
+
+// bt_ref[l][node][s][0..3] = (child0 id, argmin0, child1 id, argmin1) as f32 (sankoff.py:80-83)
+__global__ void export_bt_kernel(const int32_t* __restrict__ plan, int n_all, int n_leaves, int A,
+                                 long long n_sites, long long stride,
+                                 const uint8_t* __restrict__ arg, float* __restrict__ out) {
+  const long long l = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int j = blockIdx.y;  // node * A + s
+  if (l >= n_sites) return;
+  const int node = j / A, s = j % A;
+  float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (node >= n_leaves) {
+    const int n_int = n_all - n_leaves, k = node - n_leaves;
+    PlanView pv(plan, n_int);
+    v.x = (float)pv.raw(0)[k];
+    v.z = (float)pv.raw(1)[k];
+    v.y = (float)arg[(((size_t)k * 2 + 0) * A + s) * stride + l];
+    v.w = (float)arg[(((size_t)k * 2 + 1) * A + s) * stride + l];
+  }
+  reinterpret_cast<float4*>(out)[(size_t)l * n_all * A + j] = v;
+}
+
+// ---- traceback over a reference-layout back-pointer table -----------------------------------
+// backtrack_sankoff_jit (src/trex/sankoff.py:191-267) for callers that hold the reference's own
+// (n_all, A, 4) f32 table per site.  Top-down over node ids (children have smaller ids than
+// their parent), equivalent to the explicit stack DFS on trees.  recon: [n_sites][n_all] i32.
+__global__ void backtrack_ref_kernel(const float* __restrict__ bt, int n_all, int n_leaves, int A,
+                                     long long n_sites, const int* __restrict__ root_node,
+                                     const int* __restrict__ root_state, int* __restrict__ recon) {
+  const long long l = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= n_sites) return;
+  int* rec = recon + (size_t)l * n_all;
+  const float* b = bt + (size_t)l * n_all * A * 4;
+  for (int i = 0; i < n_all; ++i) rec[i] = -1;
+  const int root = root_node[0];
+  if (root >= n_leaves && root < n_all) rec[root] = min(max(root_state[l], 0), A - 1);
+  for (int node = min(root, n_all - 1); node >= n_leaves; --node) {
+    const int st = rec[node];
+    if (st < 0) continue;
+    const float4 info = *reinterpret_cast<const float4*>(b + ((size_t)node * A + st) * 4);
+    const int c0 = (int)info.x, s0 = (int)info.y, c1 = (int)info.z, s1 = (int)info.w;
+    // stack order of the reference: child 2 is popped (and written) before child 1
+    if (c1 >= n_leaves && c1 < node) rec[c1] = min(max(s1, 0), A - 1);
+    if (c0 >= n_leaves && c0 < node) rec[c0] = min(max(s0, 0), A - 1);
+  }
+  for (int i = 0; i < n_all; ++i)
+    if (rec[i] < 0) rec[i] = 0;
+}
+
+}  // namespace trex
+
+extern "C" {
+
+int trex_encode_leaf_states(const float* seqs, int n_leaves, int64_t n_sites, int64_t in_stride,
+                            int n_states, uint8_t* leaf_states, int64_t site_stride, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(seqs && leaf_states, "trex_encode_leaf_states: null pointer");
+  TREX_CHECK_ARG(n_leaves >= 1 && n_leaves <= 65535 && n_sites >= 1 && in_stride >= n_sites &&
+                     site_stride >= n_sites && site_stride % 16 == 0 && n_states >= 1 && n_states <= 32,
+                 "trex_encode_leaf_states: bad sizes");
+  dim3 grid((unsigned)((site_stride + 255) / 256), n_leaves);
+  encode_leaf_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(seqs, n_leaves, n_sites, in_stride,
+                                                              n_states, leaf_states, site_stride);
+  TREX_CHECK_LAUNCH("encode_leaf_kernel");
+  return TREX_OK;
+}
+
+int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                           int64_t n_sites, int64_t site_stride, int batch,
+                           const uint8_t* leaf_states, const float* dp, const uint8_t* argmin,
+                           uint8_t* anc_states, unsigned long long* edge_hist, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(plan && leaf_states && dp && argmin && anc_states, "trex_sankoff_traceback: null pointer");
+  TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves && n_states >= 1 && n_states <= 32,
+                 "trex_sankoff_traceback: bad tree sizes");
+  TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0,
+                 "trex_sankoff_traceback: site_stride must be a multiple of 16 and >= n_sites");
+  TREX_CHECK_ARG(batch >= 1 && batch <= 65535, "trex_sankoff_traceback: batch out of range");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (edge_hist) {
+    int rc = check_cuda(cudaMemsetAsync(edge_hist, 0, sizeof(unsigned long long) * batch * n_states * n_states, s),
+                        "memset edge_hist");
+    if (rc) return rc;
+  }
+  TraceParams p{plan, trex_sankoff_plan_words(n_all, n_leaves), n_all, n_leaves, n_states,
+                (long long)n_sites, (long long)site_stride, leaf_states, dp, argmin, anc_states, edge_hist};
+  constexpr int V = 4, THREADS = 128;
+  const long long nvec = (n_sites + V - 1) / V;
+  dim3 grid((unsigned)((nvec + THREADS - 1) / THREADS), batch);
+  const size_t smem = edge_hist ? sizeof(unsigned int) * n_states * n_states : 0;
+  traceback_kernel<V, THREADS><<<grid, THREADS, smem, s>>>(p);
+  TREX_CHECK_LAUNCH("traceback_kernel");
+  return TREX_OK;
+}
+
+int trex_sankoff_export_dp(int n_all, int n_leaves, int n_states, int64_t n_sites,
+                           int64_t site_stride, const uint8_t* leaf_states, const float* dp,
+                           float* dp_ref, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(leaf_states && dp && dp_ref, "trex_sankoff_export_dp: null pointer");
+  const long long J = (long long)n_all * n_states;
+  TREX_CHECK_ARG((J + 31) / 32 <= 65535, "trex_sankoff_export_dp: n_all * n_states too large");
+  dim3 grid((unsigned)((n_sites + 31) / 32), (unsigned)((J + 31) / 32));
+  export_dp_kernel<<<grid, dim3(32, 8), 0, (cudaStream_t)stream>>>(n_all, n_leaves, n_states, n_sites,
+                                                                  site_stride, leaf_states, dp, dp_ref);
+  TREX_CHECK_LAUNCH("export_dp_kernel");
+  return TREX_OK;
+}
+
+int trex_sankoff_export_recon(int n_all, int n_leaves, int64_t n_sites, int64_t site_stride,
+                              const float* leaf_seqs_f32, int64_t leaf_in_stride,
+                              const uint8_t* leaf_states, const uint8_t* anc_states,
+                              float* recon_ref, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG((leaf_seqs_f32 || leaf_states) && recon_ref, "trex_sankoff_export_recon: null pointer");
+  TREX_CHECK_ARG(n_all <= 65535, "trex_sankoff_export_recon: n_all too large");
+  dim3 grid((unsigned)((n_sites + 255) / 256), n_all);
+  export_recon_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(n_all, n_leaves, n_sites, site_stride,
+                                                               leaf_seqs_f32, leaf_in_stride, leaf_states,
+                                                               anc_states, recon_ref);
+  TREX_CHECK_LAUNCH("export_recon_kernel");
+  return TREX_OK;
+}
+
+int trex_sankoff_export_bt(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                           int64_t n_sites, int64_t site_stride, const uint8_t* argmin,
+                           float* bt_ref, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(plan && argmin && bt_ref, "trex_sankoff_export_bt: null pointer");
+  TREX_CHECK_ARG((long long)n_all * n_states <= 65535, "trex_sankoff_export_bt: n_all * n_states too large");
+  dim3 grid((unsigned)((n_sites + 255) / 256), n_all * n_states);
+  export_bt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(plan, n_all, n_leaves, n_states, n_sites,
+                                                            site_stride, argmin, bt_ref);
+  TREX_CHECK_LAUNCH("export_bt_kernel");
+  return TREX_OK;
+}
+
+int trex_sankoff_backtrack_ref(const float* bt_ref, int n_all, int n_leaves, int n_states,
+                               int64_t n_sites, const int32_t* root_node, const int32_t* root_state,
+                               int32_t* recon, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(bt_ref && root_node && root_state && recon, "trex_sankoff_backtrack_ref: null pointer");
+  TREX_CHECK_ARG(n_leaves >= 1 && n_all >= n_leaves && n_states >= 1 && n_sites >= 1,
+                 "trex_sankoff_backtrack_ref: bad sizes");
+  backtrack_ref_kernel<<<(unsigned)((n_sites + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      bt_ref, n_all, n_leaves, n_states, n_sites, root_node, root_state, recon);
+  TREX_CHECK_LAUNCH("backtrack_ref_kernel");
+  return TREX_OK;
+}
+
+}  // extern "C"

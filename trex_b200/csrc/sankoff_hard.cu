@@ -1,0 +1,301 @@
+// Hard (min-plus) Sankoff forward over the whole tree — one thread owns V consecutive sites
+// and walks the DFS post-order plan; sites are independent (src/trex/sankoff.py:97), so there
+// is no inter-thread communication at all.
+//
+// Replaces run_dp / vectorized_dp and the table + score part of run_sankoff
+// (src/trex/sankoff.py:24-97, 141-160, 187).
+//
+// HBM layout: dp[tree][k][state][site] f32, argmin[tree][k][slot][state][site] u8, leaf states
+// [leaf][site] u8.  Leaf dp rows (1e5 with a 0 at the observed state, :49-52,152) are never
+// materialised: min_t(C[s,t] + leafrow[t]) is a (A+1) x A lookup table in shared memory built
+// with exactly the reference's f32 arithmetic (row A = "no state": all-1e5).
+//
+// Two inner loops, bit-identical wherever the second is enabled:
+//  * exact-f32: v = C[s,t] + d[t]; strict '<' keeps the first minimum (jnp.argmin, :69).
+//  * packed key (integer-valued 0 <= C, max(C)*n_all < 2^18): key = 32*(C[s,t]+d[t]) + t - 15.5
+//    is exact in f32, so one fmin chain (FMNMX3 on sm_100a) yields min AND first argmin.
+#include "common.cuh"
+
+namespace trex {
+
+struct HardFwdParams {
+  const int32_t* plan;
+  size_t plan_words;
+  int n_all, n_leaves, n_states;
+  long long n_sites, stride;
+  const uint8_t* leaf;
+  const float* cost;
+  float* dp;
+  uint8_t* arg;
+  float* root_min;
+  double* total;
+  int mode;
+};
+
+template <int AP>
+struct HardSmem {
+  __align__(16) float C[AP * AP];            // [s][t], t >= A padded with 0
+  __align__(16) float leaf_cost[(AP + 1) * AP];  // [o][s]
+  uint8_t leaf_arg[(AP + 1) * AP];
+};
+
+// min and first-argmin over t of crow[t] + d[t][v]
+template <int AP, int V, bool FAST>
+__device__ __forceinline__ void minplus(const float (&crow)[AP], const float (&d)[AP][V],
+                                        float (&best)[V], int (&idx)[V]) {
+  if constexpr (FAST) {
+    // d holds keys 32*d + (t - 15.5); crow holds C (multiplied by 32 in the FFMA)
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      float b = fmaf(crow[0], 32.f, d[0][v]);
+#pragma unroll
+      for (int t = 1; t < AP; ++t) b = fminf(b, fmaf(crow[t], 32.f, d[t][v]));
+      const float val = fmaf(b, 0.03125f, 12582912.f) - 12582912.f;  // round(b/32): exact value
+      const float w = fmaf(val, -32.f, b) + 4194319.5f;              // 2^22 + t, ulp 0.5
+      best[v] = val;
+      idx[v] = (__float_as_int(w) >> 1) & 31;
+    }
+  } else {
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      float b = crow[0] + d[0][v];
+      int bi = 0;
+#pragma unroll
+      for (int t = 1; t < AP; ++t) {
+        const float x = crow[t] + d[t][v];
+        if (x < b) { b = x; bi = t; }
+      }
+      best[v] = b;
+      idx[v] = bi;
+    }
+  }
+}
+
+template <int AP, int V, bool L0, bool L1, bool FAST>
+__device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long long stride,
+                                          const float* __restrict__ dp, const uint8_t* __restrict__ leaf,
+                                          int n_leaves, int c0, int c1, float* __restrict__ out,
+                                          uint8_t* __restrict__ arg_out, bool is_root,
+                                          float (&rmin)[V], const int (&o0)[V], const int (&o1)[V]) {
+  float d0[L0 ? 1 : AP][V], d1[L1 ? 1 : AP][V];
+  if constexpr (!L0) {
+    const float* src = dp + (size_t)(c0 - n_leaves) * A * stride;
+#pragma unroll
+    for (int t = 0; t < AP; ++t) {
+      if (t < A) ld_f<V>(src + (size_t)t * stride, d0[t]);
+      else {
+#pragma unroll
+        for (int v = 0; v < V; ++v) d0[t][v] = INFINITY;
+      }
+    }
+  }
+  if constexpr (!L1) {
+    const float* src = dp + (size_t)(c1 - n_leaves) * A * stride;
+#pragma unroll
+    for (int t = 0; t < AP; ++t) {
+      if (t < A) ld_f<V>(src + (size_t)t * stride, d1[t]);
+      else {
+#pragma unroll
+        for (int v = 0; v < V; ++v) d1[t][v] = INFINITY;
+      }
+    }
+  }
+  if constexpr (FAST) {
+#pragma unroll
+    for (int t = 0; t < AP; ++t)
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        if constexpr (!L0) d0[t][v] = fmaf(d0[t][v], 32.f, (float)t - 15.5f);
+        if constexpr (!L1) d1[t][v] = fmaf(d1[t][v], 32.f, (float)t - 15.5f);
+      }
+  }
+#pragma unroll 2
+  for (int s = 0; s < A; ++s) {
+    float crow[AP];
+    if constexpr (!L0 || !L1) {
+      if constexpr (AP % 4 == 0) {
+#pragma unroll
+        for (int t = 0; t < AP; t += 4) {
+          const float4 c4 = *reinterpret_cast<const float4*>(&sm.C[s * AP + t]);
+          crow[t] = c4.x; crow[t + 1] = c4.y; crow[t + 2] = c4.z; crow[t + 3] = c4.w;
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < AP; ++t) crow[t] = sm.C[s * AP + t];
+      }
+    }
+    float b0[V], b1[V], o[V];
+    int i0[V], i1[V];
+    if constexpr (L0) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        b0[v] = sm.leaf_cost[o0[v] * AP + s];
+        i0[v] = sm.leaf_arg[o0[v] * AP + s];
+      }
+    } else {
+      minplus<AP, V, FAST>(crow, d0, b0, i0);
+    }
+    if constexpr (L1) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        b1[v] = sm.leaf_cost[o1[v] * AP + s];
+        i1[v] = sm.leaf_arg[o1[v] * AP + s];
+      }
+    } else {
+      minplus<AP, V, FAST>(crow, d1, b1, i1);
+    }
+#pragma unroll
+    for (int v = 0; v < V; ++v) o[v] = b0[v] + b1[v];  // (0 + cost0) + cost1, sankoff.py:70
+    st_f<V>(out + (size_t)s * stride, o);
+    if (arg_out) {
+      st_u8_stream<V>(arg_out + (size_t)s * stride, i0);
+      st_u8_stream<V>(arg_out + ((size_t)A + s) * stride, i1);
+    }
+    if (is_root) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], o[v]);
+    }
+  }
+}
+
+template <int AP, int V, int THREADS>
+__global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p) {
+  __shared__ HardSmem<AP> sm;
+  const int A = p.n_states;
+  const int tid = threadIdx.x;
+  const int tree = blockIdx.y;
+  const int n_int = p.n_all - p.n_leaves;
+  PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+
+  // ---- prologue: cost matrix, leaf lookup table, fast-path eligibility --------------------
+  bool c_ok = true;
+  for (int i = tid; i < AP * AP; i += THREADS) {
+    const int s = i / AP, t = i % AP;
+    float c = 0.f;
+    if (s < A && t < A) {
+      c = __ldg(p.cost + s * A + t);
+      c_ok = c_ok && (c >= 0.f) && (c == truncf(c)) && (c * (float)p.n_all < 262000.f);
+    }
+    sm.C[i] = c;
+  }
+  const int fast_ok = __syncthreads_and(c_ok) && p.mode == TREX_MODE_AUTO &&
+                      !(plan.hdr()[3] & TREX_PLAN_HAS_SENTINEL_CHILD);
+  for (int i = tid; i < (A + 1) * A; i += THREADS) {
+    const int o = i / A, s = i % A;
+    float b = sm.C[s * AP + 0] + (o == 0 ? 0.f : kSentinel);  // sankoff.py:67 on a leaf row
+    int bi = 0;
+    for (int t = 1; t < A; ++t) {
+      const float x = sm.C[s * AP + t] + (o == t ? 0.f : kSentinel);
+      if (x < b) { b = x; bi = t; }
+    }
+    sm.leaf_cost[o * AP + s] = b;
+    sm.leaf_arg[o * AP + s] = (uint8_t)bi;
+  }
+  __syncthreads();
+
+  const long long site0 = ((long long)blockIdx.x * THREADS + tid) * V;
+  const bool active = site0 < p.n_sites;
+  float rmin[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) rmin[v] = INFINITY;
+
+  if (active) {
+    float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
+    uint8_t* arg = p.arg ? p.arg + (size_t)tree * n_int * 2 * A * p.stride + site0 : nullptr;
+    const uint8_t* leaf = p.leaf + site0;
+    const int32_t* order = plan.order();
+    const int32_t* ch0 = plan.child(0);
+    const int32_t* ch1 = plan.child(1);
+    bool bad = false;  // an out-of-range leaf state puts ~1e5 values into internal rows
+    for (int i = 0; i < n_int; ++i) {
+      const int node = __ldg(order + i);
+      const int k = node - p.n_leaves;
+      const int c0 = __ldg(ch0 + k), c1 = __ldg(ch1 + k);
+      const bool l0 = c0 < p.n_leaves, l1 = c1 < p.n_leaves;
+      int o0[V], o1[V];
+#pragma unroll
+      for (int v = 0; v < V; ++v) o0[v] = o1[v] = A;
+      if (l0 && c0 >= 0) {
+        ld_u8<V>(leaf + (size_t)c0 * p.stride, o0);
+#pragma unroll
+        for (int v = 0; v < V; ++v) { if (o0[v] >= A) { o0[v] = A; bad = true; } }
+      }
+      if (l1 && c1 >= 0) {
+        ld_u8<V>(leaf + (size_t)c1 * p.stride, o1);
+#pragma unroll
+        for (int v = 0; v < V; ++v) { if (o1[v] >= A) { o1[v] = A; bad = true; } }
+      }
+      float* out = dp + (size_t)k * A * p.stride;
+      uint8_t* aout = arg ? arg + (size_t)k * 2 * A * p.stride : nullptr;
+      const bool is_root = node == p.n_all - 1;
+#define TREX_NODE(L0, L1, F) \
+  hard_node<AP, V, L0, L1, F>(sm, A, p.stride, dp, leaf, p.n_leaves, c0, c1, out, aout, is_root, rmin, o0, o1)
+      if (l0 && l1) {
+        TREX_NODE(true, true, false);
+      } else if (fast_ok && !bad) {
+        if (l0) TREX_NODE(true, false, true);
+        else if (l1) TREX_NODE(false, true, true);
+        else TREX_NODE(false, false, true);
+      } else {
+        if (l0) TREX_NODE(true, false, false);
+        else if (l1) TREX_NODE(false, true, false);
+        else TREX_NODE(false, false, false);
+      }
+#undef TREX_NODE
+    }
+    if (p.root_min) st_f<V>(p.root_min + (size_t)tree * p.stride + site0, rmin);
+  }
+  if (p.total) {
+    double acc = 0.0;
+    if (active) {
+#pragma unroll
+      for (int v = 0; v < V; ++v)
+        if (site0 + v < p.n_sites) acc += (double)rmin[v];
+    }
+    block_atomic_add(acc, p.total + tree);
+  }
+}
+
+template <int AP, int V>
+static int launch_hard(const HardFwdParams& p, int batch, cudaStream_t s) {
+  constexpr int THREADS = 128;
+  const long long nvec = (p.n_sites + V - 1) / V;
+  dim3 grid((unsigned)((nvec + THREADS - 1) / THREADS), batch);
+  hard_fwd_kernel<AP, V, THREADS><<<grid, THREADS, 0, s>>>(p);
+  return check_cuda(cudaPeekAtLastError(), "hard_fwd_kernel");
+}
+
+}  // namespace trex
+
+extern "C" int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                                     int64_t n_sites, int64_t site_stride, int batch,
+                                     const uint8_t* leaf_states, const float* cost, float* dp,
+                                     uint8_t* argmin, float* root_min, double* total, int mode,
+                                     void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(plan && leaf_states && cost && dp, "trex_sankoff_hard_fwd: null pointer");
+  TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves, "trex_sankoff_hard_fwd: need n_all > n_leaves >= 1");
+  TREX_CHECK_ARG(n_states >= 1 && n_states <= 32, "trex_sankoff_hard_fwd: n_states %d not in 1..32", n_states);
+  TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0,
+                 "trex_sankoff_hard_fwd: site_stride must be a multiple of 16 and >= n_sites");
+  TREX_CHECK_ARG(batch >= 1 && batch <= 65535, "trex_sankoff_hard_fwd: batch out of range");
+  TREX_CHECK_ARG(mode == TREX_MODE_AUTO || mode == TREX_MODE_GENERAL, "trex_sankoff_hard_fwd: bad mode");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (total) {
+    int rc = check_cuda(cudaMemsetAsync(total, 0, sizeof(double) * batch, s), "memset total");
+    if (rc) return rc;
+  }
+  HardFwdParams p{plan, trex_sankoff_plan_words(n_all, n_leaves), n_all, n_leaves, n_states,
+                  (long long)n_sites, (long long)site_stride, leaf_states, cost, dp, argmin,
+                  root_min, total, mode};
+  const int A = n_states;
+  if (A <= 2) return launch_hard<2, 4>(p, batch, s);
+  if (A <= 4) return launch_hard<4, 4>(p, batch, s);
+  if (A <= 8) return launch_hard<8, 2>(p, batch, s);
+  if (A <= 20) {
+    // few sites per GPU (site-sharded runs): one site per thread keeps more warps in flight
+    if (n_sites * (long long)batch < 148LL * 512) return launch_hard<20, 1>(p, batch, s);
+    return launch_hard<20, 2>(p, batch, s);
+  }
+  return launch_hard<32, 1>(p, batch, s);
+}
