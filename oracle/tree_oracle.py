@@ -105,6 +105,8 @@ def naive_compute_soft_cost(sequences, adjacency, cost_matrix=None, dtype=np.flo
   A = np.asarray(adjacency, dtype=dtype)
   Q = S.shape[-1]
   C = np.eye(Q, dtype=dtype) if cost_matrix is None else np.asarray(cost_matrix, dtype=dtype)
+  if C.ndim == 1:
+    C = np.diag(C)  # compute_soft_cost's (Q,) form is a diagonal cost (tree.py:250-251)
   total = dtype(0)
   for i in range(S.shape[0]):  # row-blocked so the (N,N,L,Q) tensor is never materialised
     diff = S[i][None] - S  # (N, L, Q)

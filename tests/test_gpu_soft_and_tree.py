@@ -137,8 +137,11 @@ def test_tree_cost_value_and_grads(N, L, Q, ak, ckind):
   assert _relerr(dA.cpu().numpy(), dA64) <= RTOL
   if C is not None:
     assert _relerr(dC.cpu().numpy(), dC64) <= RTOL
-  naive = to.naive_compute_soft_cost(S, adj, C)
-  assert abs(float(cost) - naive) <= bound + 1e-9 * abs(naive)
+  if ckind != "asym":
+    # the direct (N,N,L,Q) form of benchmark_tree_cost.py:10-32 equals tree.py's expanded form only
+    # for symmetric C; the library follows tree.py (the shipped function) for asymmetric C
+    naive = to.naive_compute_soft_cost(S, adj, C)
+    assert abs(float(cost) - naive) <= bound + 1e-9 * abs(naive)
 
 
 def test_tree_cost_autograd_matches_reference_signatures():
