@@ -151,6 +151,34 @@ TREX_API int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const f
                            float* d_seqs, float* d_adj, float* d_cost, void* workspace,
                            void* stream);
 
+/* ---- the small operators around the tree cost and their reverse modes ------
+ * T3 update_seq (src/trex/tree.py:110-130; stacked twin src/trex/evals/benchmark.py:210-232):
+ *    seqs_ancestor_rows [n_anc][L][Q] = softmax(logits * temperature) over the last axis. */
+TREX_API int trex_update_seq_fwd(const float* logits, int n_ancestors, int64_t n_sites, int n_states,
+                        float temperature, float* seqs_ancestor_rows, void* stream);
+TREX_API int trex_update_seq_bwd(const float* seqs_ancestor_rows, const float* d_seqs_ancestor_rows,
+                        int n_ancestors, int64_t n_sites, int n_states, float temperature,
+                        float* d_logits, void* stream);
+/* T4 update_tree (src/trex/tree.py:50-107): tree_params/gumbel_noise/gates [(N-1)][n_anc]
+ *    (noise and gates may be NULL; jax.random streams are not reproducible outside JAX, so the
+ *    Gumbel draw is an input), adjacency [N][N] out, rows sum to 1. */
+TREX_API int trex_update_tree_fwd(const float* tree_params, const float* gumbel_noise, const float* gates,
+                         float temperature, int n_nodes, int n_leaves, float* adjacency, void* stream);
+TREX_API int trex_update_tree_bwd(const float* adjacency, const float* d_adjacency, const float* gates,
+                         float temperature, int n_nodes, int n_leaves, float* d_tree_params, void* stream);
+/* T5 enforce_graph_constraints (src/trex/tree.py:133-160); d_adjacency [N][N] out or NULL;
+ *    scratch: one f64. */
+TREX_API int trex_graph_constraint(const float* adjacency, int n_nodes, float scaling_factor, float* out_loss,
+                          float* d_adjacency, double* scratch, void* stream);
+/* T7 discretize_tree_topology (src/trex/tree.py:31-47); parent_scratch [N] i32. */
+TREX_API int trex_discretize_topology(const float* adjacency, int n_nodes, int32_t* parent_scratch,
+                             float* one_hot, void* stream);
+/* T6 compute_cost (src/trex/tree.py:269-296); state_scratch [N][L] i32, parent_scratch [N] i32,
+ *    acc_scratch one f64. */
+TREX_API int trex_compute_cost(const float* seqs_one_hot, const float* adjacency, const float* subst,
+                      int n_nodes, int64_t n_sites, int n_states, int32_t* state_scratch,
+                      int32_t* parent_scratch, double* acc_scratch, float* out_cost, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,13 @@ SIGNATURES = {
   "trex_sankoff_soft_bwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
   "trex_tree_cost_workspace_bytes": (C.c_size_t, [_i, _i64, _i]),
   "trex_tree_cost_fwd_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+  "trex_update_seq_fwd": (_i, [_vp, _i, _i64, _i, _f, _vp, _vp]),
+  "trex_update_seq_bwd": (_i, [_vp, _vp, _i, _i64, _i, _f, _vp, _vp]),
+  "trex_update_tree_fwd": (_i, [_vp, _vp, _vp, _f, _i, _i, _vp, _vp]),
+  "trex_update_tree_bwd": (_i, [_vp, _vp, _vp, _f, _i, _i, _vp, _vp]),
+  "trex_graph_constraint": (_i, [_vp, _i, _f, _vp, _vp, _vp, _vp]),
+  "trex_discretize_topology": (_i, [_vp, _i, _vp, _vp, _vp]),
+  "trex_compute_cost": (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp]),
 }
 
 _lib = None
