@@ -11,24 +11,10 @@
 // (s,t) pairs in registers and sweeps the CTA's sites (lane = site, conflict-free), so the
 // pair sums live in registers for the whole tree walk and are flushed with f64 atomics.
 #include "common.cuh"
+#include "soft_bwd_params.cuh"
 
 namespace trex {
 
-struct SoftBwdParams {
-  const int32_t* plan;
-  size_t plan_words;
-  int n_all, n_leaves, n_states;
-  long long n_sites, stride;
-  const uint8_t* leaf;
-  const float* leaf_cost;
-  const float* cost;
-  float T;
-  const float* dp;
-  const float* gscale;
-  float* gbar;
-  float* dleaf;
-  double* dcost;
-};
 
 template <int AP> struct DcTile;  // RS x CS pair block per warp, NBLK blocks cover AP x AP
 template <> struct DcTile<2> { static constexpr int RS = 2, CS = 2; };
@@ -86,6 +72,7 @@ __global__ void __launch_bounds__(THREADS) soft_bwd_kernel(const SoftBwdParams p
     if (WANT_DC) sP[i] = 0.f;
   }
   const int expdom = __syncthreads_and(c_ok);
+  if (p.only_direct && expdom) return;  // soft_bwd_warp_kernel owns this case
   for (int s = tid; s < AP; s += THREADS) {
     float z = 0.f;
     for (int t = 0; t < AP; ++t) z += sK[s * AP + t];
@@ -414,8 +401,15 @@ extern "C" int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leave
   }
   SoftBwdParams p{plan, trex_sankoff_plan_words(n_all, n_leaves), n_all, n_leaves, n_states,
                   (long long)n_sites, (long long)site_stride, leaf_states, leaf_cost, cost,
-                  temperature, dp, gscale, gbar, dleaf, dcost};
+                  temperature, dp, gscale, gbar, dleaf, dcost, 0};
   const int A = n_states;
+  if (A <= 20) {
+    // Device-side dispatch (the cost matrix is device data): the warp-autonomous exp-domain kernel
+    // returns at once when max|C|/T > 80, the direct-evaluation kernel returns at once otherwise.
+    int rc = launch_soft_bwd_warp(p, batch, s);
+    if (rc) return rc;
+    p.only_direct = 1;
+  }
   if (A <= 2) return launch_soft_bwd<2, 2, 256>(p, batch, s);
   if (A <= 4) return launch_soft_bwd<4, 2, 256>(p, batch, s);
   if (A <= 8) return launch_soft_bwd<8, 1, 256>(p, batch, s);
