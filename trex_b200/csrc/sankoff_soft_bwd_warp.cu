@@ -47,6 +47,27 @@ __device__ __forceinline__ void sts_v(float* p, const float (&v)[V]) {
   st_f<V>(p, v);
 }
 
+// single-MUFU forms: results below 2^-126 flush to zero, which is what the callers want
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// global -> shared copy of V floats without a register round trip; bytes past `src_bytes` are
+// zero-filled (masks the cotangent of lanes past the end)
+template <int V>
+__device__ __forceinline__ void cp_async_v(float* smem_dst, const float* gsrc, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], %2, %3;" ::"r"(d), "l"(gsrc), "n"(4 * V), "r"(src_bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ float rcp_fast(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 }  // namespace
 
 template <int AP, int V, int W, bool WANT_DC>
@@ -92,15 +113,23 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   float* sE = sR + AP * PITCH;
   double* sAcc = reinterpret_cast<double*>(sE + AP * PITCH);
 
-  const long long site0 = (gw * 32 + lane) * V;
-  const bool active = site0 < p.n_sites;
+
+  // Lanes past the end mirror the last valid site vector: their loads stay in bounds and finite,
+  // their stores are predicated off and their cotangent is masked to zero (okf).
+  const long long site_raw = (gw * 32 + lane) * V;
+  const bool active = site_raw < p.n_sites;
+  const long long site0 = active ? site_raw : ((p.n_sites - 1) / V) * V;
   bool ok[V];
 #pragma unroll
-  for (int v = 0; v < V; ++v) ok[v] = site0 + v < p.n_sites;
+  for (int v = 0; v < V; ++v) ok[v] = site_raw + v < p.n_sites;
+  int ok_bytes = 0;
+#pragma unroll
+  for (int v = 0; v < V; ++v) ok_bytes += ok[v] ? 4 : 0;
   const float gs = p.gscale ? __ldg(p.gscale) : 1.f;
-  const float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
-  float* gbar = p.gbar + (size_t)tree * n_int * A * p.stride + site0;
-  float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * p.stride + site0 : nullptr;
+  const size_t stride = (size_t)p.stride;
+  const float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
+  float* gbar = p.gbar + (size_t)tree * n_int * A * stride + site0;
+  float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * stride + site0 : nullptr;
   const int32_t* order = plan.order();
   const int32_t* ch0 = plan.child(0);
   const int32_t* ch1 = plan.child(1);
@@ -111,6 +140,8 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   // pair-tile ownership in the sweep
   const int tile = lane % NT, sg = lane / NT;
   const int rb = tile / Cfg::TC, cb = tile % Cfg::TC;
+  const float* rbase = sR + rb * RS * PITCH + sg * 4;
+  const float* ebase = sE + cb * CS * PITCH + sg * 4;
   float acc[RS][CS], accG[RS][CS];  // r-space (times K at flush) and g-space pair sums
 #pragma unroll
   for (int a = 0; a < RS; ++a)
@@ -118,315 +149,323 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
     for (int b = 0; b < CS; ++b) acc[a][b] = accG[a][b] = 0.f;
   if constexpr (WANT_DC) {
     for (int i = lane; i < AP * AP; i += 32) sAcc[i] = 0.0;
+    for (int i = lane; i < 2 * AP * PITCH; i += 32) sR[i] = 0.f;  // pad rows / columns stay zero
+    __syncwarp();
   }
 
-  auto sweep = [&](float (&dst)[RS][CS]) {
-    const float* rbase = sR + rb * RS * PITCH + sg * 4;
-    const float* ebase = sE + cb * CS * PITCH + sg * 4;
-#pragma unroll 2
-    for (int it = 0; it < Cfg::NCH; ++it) {
-      float4 rr[RS], ee[CS];
-#pragma unroll
-      for (int a = 0; a < RS; ++a) rr[a] = *reinterpret_cast<const float4*>(rbase + a * PITCH + it * (SG * 4));
-#pragma unroll
-      for (int b = 0; b < CS; ++b) ee[b] = *reinterpret_cast<const float4*>(ebase + b * PITCH + it * (SG * 4));
-#pragma unroll
-      for (int a = 0; a < RS; ++a)
-#pragma unroll
-        for (int b = 0; b < CS; ++b) {
-          float x = dst[a][b];
-          x = fmaf(rr[a].x, ee[b].x, x);
-          x = fmaf(rr[a].y, ee[b].y, x);
-          x = fmaf(rr[a].z, ee[b].z, x);
-          x = fmaf(rr[a].w, ee[b].w, x);
-          dst[a][b] = x;
-        }
-    }
-  };
-
-  auto flush = [&](float (&src)[RS][CS], bool rspace) {
-#pragma unroll
-    for (int a = 0; a < RS; ++a)
-#pragma unroll
-      for (int b = 0; b < CS; ++b) {
-        float v = src[a][b];
-        src[a][b] = 0.f;
-#pragma unroll
-        for (int o = NT; o < 32; o <<= 1) v += __shfl_xor_sync(kFull, v, o);
-        if (sg == 0) {
-          const int idx = (rb * RS + a) * AP + cb * CS + b;
-          sAcc[idx] += (double)v * (rspace ? (double)sK[idx] : 1.0);
-        }
-      }
-  };
-
   // ---- nodes the root does not reach get zero cotangent; root: gscale * softmax(-dp/T) --------
-  if (active) {
+  {
     float zero[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) zero[v] = 0.f;
-    for (int i = n_reach; i < n_int; ++i) {
-      float* row = gbar + (size_t)(__ldg(order + i) - p.n_leaves) * A * p.stride;
-      for (int s = 0; s < A; ++s) st_f<V>(row + (size_t)s * p.stride, zero);
-    }
-    float x[AP][V];
-    const float* rrow = dp + (size_t)(n_int - 1) * A * p.stride;
-#pragma unroll
-    for (int s = 0; s < AP; ++s) {
-      if (s < A) ld_f<V>(rrow + (size_t)s * p.stride, x[s]);
-      else {
-#pragma unroll
-        for (int v = 0; v < V; ++v) x[s][v] = INFINITY;
+    if (active) {
+      for (int i = n_reach; i < n_int; ++i) {
+        float* row = gbar + (size_t)(__ldg(order + i) - p.n_leaves) * A * stride;
+        for (int s = 0; s < A; ++s) st_f<V>(row + s * stride, zero);
       }
     }
+    const float* rrow = dp + (size_t)(n_int - 1) * A * stride;
+    float* grow = gbar + (size_t)(n_int - 1) * A * stride;
+    float mm[V], z[V];
 #pragma unroll
-    for (int v = 0; v < V; ++v) {
-      float mm = x[0][v];
+    for (int v = 0; v < V; ++v) { mm[v] = INFINITY; z[v] = 0.f; }
+    for (int s = 0; s < A; ++s) {
+      float x[V];
+      ld_f<V>(rrow + s * stride, x);
 #pragma unroll
-      for (int s = 1; s < AP; ++s) mm = fminf(mm, x[s][v]);
-      float z = 0.f;
-#pragma unroll
-      for (int s = 0; s < AP; ++s) { x[s][v] = exp2f((mm - x[s][v]) * c1); z += x[s][v]; }
-      const float inv = gs / z;
-#pragma unroll
-      for (int s = 0; s < AP; ++s) x[s][v] *= inv;
+      for (int v = 0; v < V; ++v) mm[v] = fminf(mm[v], x[v]);
     }
-    float* grow = gbar + (size_t)(n_int - 1) * A * p.stride;
+    for (int s = 0; s < A; ++s) {
+      float x[V];
+      ld_f<V>(rrow + s * stride, x);
 #pragma unroll
-    for (int s = 0; s < AP; ++s)
-      if (s < A) st_f<V>(grow + (size_t)s * p.stride, x[s]);
+      for (int v = 0; v < V; ++v) z[v] += exp2f((mm[v] - x[v]) * c1);
+    }
+    for (int s = 0; s < A; ++s) {
+      float x[V];
+      ld_f<V>(rrow + s * stride, x);
+#pragma unroll
+      for (int v = 0; v < V; ++v) x[v] = exp2f((mm[v] - x[v]) * c1) * (gs / z[v]);
+      if (active) st_f<V>(grow + s * stride, x);
+    }
   }
 
   int since_flush = 0;
-  for (int i = n_reach - 1; i >= 0; --i) {
+  for (int i = n_reach - 1;; --i) {
+    if constexpr (WANT_DC) {
+      // f32 pair sums -> warp-private f64 table (K applied to the r-space part); single code site
+      if (i < 0 || since_flush == kFlush) {
+        since_flush = 0;
+#pragma unroll
+        for (int a = 0; a < RS; ++a)
+#pragma unroll
+          for (int b = 0; b < CS; ++b) {
+            float vr = acc[a][b], vg = accG[a][b];
+            acc[a][b] = accG[a][b] = 0.f;
+#pragma unroll
+            for (int o = NT; o < 32; o <<= 1) {
+              vr += __shfl_xor_sync(kFull, vr, o);
+              vg += __shfl_xor_sync(kFull, vg, o);
+            }
+            if (sg == 0) {
+              const int idx = (rb * RS + a) * AP + cb * CS + b;
+              sAcc[idx] += (double)vr * (double)sK[idx] + (double)vg;
+            }
+          }
+      }
+    }
+    if (i < 0) break;
+    ++since_flush;
     const int node = __ldg(order + i);
     const int k = node - p.n_leaves;
-    const float* grow = gbar + (size_t)k * A * p.stride;  // cotangent of this node (own earlier store)
-    int cc[2] = {__ldg(ch0 + k), __ldg(ch1 + k)};
-    bool gen[2];
-#pragma unroll
-    for (int slot = 0; slot < 2; ++slot)
-      gen[slot] = cc[slot] >= p.n_leaves || (cc[slot] >= 0 && p.leaf_cost != nullptr);
+    const float* grow = gbar + (size_t)k * A * stride;  // cotangent of this node (own earlier store)
+    const int cc0 = __ldg(ch0 + k), cc1 = __ldg(ch1 + k);
+    const bool gen0 = cc0 >= p.n_leaves || (cc0 >= 0 && p.leaf_cost != nullptr);
+    const bool gen1 = cc1 >= p.n_leaves || (cc1 >= 0 && p.leaf_cost != nullptr);
+    int o0[V], o1[V];  // observed states of children handled in g space (A: none, -1: not handled)
+    bool ns0 = false, ns1 = false;
 
-    // ---- children given as observed states (or missing): one g-space sweep for both ----------
-    if (!gen[0] || !gen[1]) {
-      int o[2][V];  // observed state; A = leaf without state / missing child; -1 = slot not handled here
-      bool nostate = false;
+    // phases: 0 = children given as states (one g-space sweep for both); 1,2 = stateless leaves /
+    // missing children of slot 0,1 (rare); 3,4 = children with a cost row.  One sweep site.
+#pragma unroll 1
+    for (int ph = 0; ph < 5; ++ph) {
+      bool gspace = false;
+      if (ph == 0) {
+        if (gen0 && gen1) { ph = 2; continue; }
+        gspace = true;
 #pragma unroll
-      for (int slot = 0; slot < 2; ++slot) {
-#pragma unroll
-        for (int v = 0; v < V; ++v) o[slot][v] = gen[slot] ? -1 : A;
-        if (!gen[slot] && cc[slot] >= 0 && active) {
-          ld_u8<V>(p.leaf + (size_t)cc[slot] * p.stride + site0, o[slot]);
-#pragma unroll
-          for (int v = 0; v < V; ++v) o[slot][v] = min(o[slot][v], A);
-        }
-#pragma unroll
-        for (int v = 0; v < V; ++v) nostate = nostate || (o[slot][v] == A && ok[v]);
-      }
-      float tot[V];
-#pragma unroll
-      for (int v = 0; v < V; ++v) tot[v] = 0.f;
-#pragma unroll 4
-      for (int s = 0; s < A; ++s) {
-        float gv[V], cnt[V];
-#pragma unroll
-        for (int v = 0; v < V; ++v) gv[v] = 0.f;
-        if (active) ld_f<V>(grow + (size_t)s * p.stride, gv);
+        for (int v = 0; v < V; ++v) { o0[v] = gen0 ? -1 : A; o1[v] = gen1 ? -1 : A; }
+        if (!gen0 && cc0 >= 0) ld_u8<V>(p.leaf + (size_t)cc0 * stride + site0, o0);
+        if (!gen1 && cc1 >= 0) ld_u8<V>(p.leaf + (size_t)cc1 * stride + site0, o1);
+        bool n0 = false, n1 = false;
 #pragma unroll
         for (int v = 0; v < V; ++v) {
-          gv[v] = ok[v] ? gv[v] : 0.f;
-          tot[v] += gv[v];
-          cnt[v] = (o[0][v] == s ? 1.f : 0.f) + (o[1][v] == s ? 1.f : 0.f);
+          o0[v] = min(o0[v], A);
+          o1[v] = min(o1[v], A);
+          n0 = n0 || (o0[v] == A && ok[v]);
+          n1 = n1 || (o1[v] == A && ok[v]);
         }
-        if constexpr (WANT_DC) {
-          sts_v<V>(myR + s * PITCH, gv);
-          sts_v<V>(myE + s * PITCH, cnt);
-        }
-      }
-      // d total / d leaf_cost of leaves with a state: all of the parent's mass on the observed state
+        ns0 = __any_sync(kFull, n0);
+        ns1 = __any_sync(kFull, n1);
+        float tot[V];
 #pragma unroll
-      for (int slot = 0; slot < 2; ++slot) {
-        if (gen[slot] || cc[slot] < 0 || !dleaf || !active) continue;
-        float* dst = dleaf + (size_t)cc[slot] * A * p.stride;
-        for (int t = 0; t < A; ++t) {
-          float out[V];
+        for (int v = 0; v < V; ++v) tot[v] = 0.f;
+#pragma unroll 4
+        for (int s = 0; s < A; ++s) {
+          float gv[V], cnt[V];
+          ld_f<V>(grow + s * stride, gv);
 #pragma unroll
-          for (int v = 0; v < V; ++v) out[v] = o[slot][v] == t ? tot[v] : 0.f;
-          st_f_stream<V>(dst + (size_t)t * p.stride, out);
-        }
-      }
-      if constexpr (WANT_DC) {
-        __syncwarp();
-        sweep(accG);
-        __syncwarp();
-      }
-      // leaves without a state / missing children: the all-1e5 row has uniform e, w = K / rowsum(K)
-      if (__any_sync(kFull, nostate)) {
-#pragma unroll
-        for (int slot = 0; slot < 2; ++slot) {
-          bool ns[V];
-          bool any = false;
-#pragma unroll
-          for (int v = 0; v < V; ++v) { ns[v] = o[slot][v] == A && ok[v]; any = any || ns[v]; }
-          if (!__any_sync(kFull, any)) continue;
-          float* dst = (cc[slot] >= 0 && dleaf) ? dleaf + (size_t)cc[slot] * A * p.stride : nullptr;
-          for (int s = 0; s < A; ++s) {
-            float gv[V], one[V];
-#pragma unroll
-            for (int v = 0; v < V; ++v) gv[v] = 0.f;
-            if (active) ld_f<V>(grow + (size_t)s * p.stride, gv);
-#pragma unroll
-            for (int v = 0; v < V; ++v) {
-              gv[v] = ns[v] ? __fdividef(gv[v], sRowK[s]) : 0.f;
-              one[v] = ns[v] ? 1.f : 0.f;
-            }
-            sts_v<V>(myR + s * PITCH, gv);
-            sts_v<V>(myE + s * PITCH, one);
-          }
-          if (dst && any) {
-            for (int t = 0; t < A; ++t) {
-              float out[V];
-              ld_f<V>(dst + (size_t)t * p.stride, out);  // hot lanes keep what was stored above
-#pragma unroll
-              for (int v = 0; v < V; ++v) {
-                if (!ns[v]) continue;
-                float a = 0.f;
-                for (int s = 0; s < A; ++s) a = fmaf(sKt[t * AP + s], myR[s * PITCH + v], a);
-                out[v] = a;
-              }
-              st_f<V>(dst + (size_t)t * p.stride, out);
-            }
+          for (int v = 0; v < V; ++v) {
+            gv[v] = ok[v] ? gv[v] : 0.f;
+            tot[v] += gv[v];
+            cnt[v] = (o0[v] == s ? 1.f : 0.f) + (o1[v] == s ? 1.f : 0.f);
           }
           if constexpr (WANT_DC) {
-            __syncwarp();
-            sweep(acc);
-            __syncwarp();
+            sts_v<V>(myR + s * PITCH, gv);
+            sts_v<V>(myE + s * PITCH, cnt);
           }
         }
-      }
-    }
-
-    // ---- children with a cost row (internal nodes, soft leaves) --------------------------------
-#pragma unroll 1
-    for (int slot = 0; slot < 2; ++slot) {
-      if (!(slot ? gen[1] : gen[0])) continue;
-      const int c = slot ? cc[1] : cc[0];
-      const float* src;
-      float* dst;
-      if (c >= p.n_leaves) {
-        src = dp + (size_t)(c - p.n_leaves) * A * p.stride;
-        dst = gbar + (size_t)(c - p.n_leaves) * A * p.stride;
-      } else {
-        src = p.leaf_cost + (size_t)c * A * p.stride + site0;
-        dst = dleaf ? dleaf + (size_t)c * A * p.stride : nullptr;
-      }
-      float e[AP][V];
+        // d total / d leaf_cost of leaves with a state: all of the parent's mass on that state
+        if (dleaf && active) {
 #pragma unroll
-      for (int t = 0; t < AP; ++t) {
+          for (int slot = 0; slot < 2; ++slot) {
+            const int c = slot ? cc1 : cc0;
+            if ((slot ? gen1 : gen0) || c < 0) continue;
+            float* dst = dleaf + (size_t)c * A * stride;
+            for (int t = 0; t < A; ++t) {
+              float out[V];
 #pragma unroll
-        for (int v = 0; v < V; ++v) e[t][v] = t < A ? 0.f : INFINITY;
-        if (t < A && active) ld_f_stream<V>(src + (size_t)t * p.stride, e[t]);
-      }
+              for (int v = 0; v < V; ++v) out[v] = (slot ? o1[v] : o0[v]) == t ? tot[v] : 0.f;
+              st_f_stream<V>(dst + t * stride, out);
+            }
+          }
+        }
+      } else if (ph < 3) {
+        // all-1e5 child row: uniform e, softmin weights K / rowsum(K)  (r-space)
+        const int slot = ph - 1;
+        if (!(slot ? ns1 : ns0)) continue;
+        const int c = slot ? cc1 : cc0;
+        bool ns[V];
+        bool any = false;
 #pragma unroll
-      for (int v = 0; v < V; ++v) {
-        float mm = e[0][v];
+        for (int v = 0; v < V; ++v) { ns[v] = (slot ? o1[v] : o0[v]) == A && ok[v]; any = any || ns[v]; }
+        for (int s = 0; s < A; ++s) {
+          float gv[V], one[V];
+          ld_f<V>(grow + s * stride, gv);
 #pragma unroll
-        for (int t = 1; t < AP; ++t) mm = fminf(mm, e[t][v]);
-        mm = ok[v] ? mm : 0.f;
-#pragma unroll
-        for (int t = 0; t < AP; ++t) e[t][v] = ok[v] ? exp2f((mm - e[t][v]) * c1) : 0.f;
-      }
-#pragma unroll
-      for (int t = 0; t < AP; ++t) sts_v<V>(myE + t * PITCH, e[t]);
-      // r[s] = g[s] / Z[s]  -> staged; never kept in registers
-#pragma unroll 4
-      for (int s = 0; s < A; ++s) {
-        float gv[V], z[V];
-#pragma unroll
-        for (int v = 0; v < V; ++v) { gv[v] = 0.f; z[v] = 0.f; }
-        if (active) ld_f<V>(grow + (size_t)s * p.stride, gv);
-        const float* krow = sK + s * AP;
-        if constexpr (AP % 4 == 0) {
-#pragma unroll
-          for (int t = 0; t < AP; t += 4) {
-            const float4 k4 = *reinterpret_cast<const float4*>(krow + t);
+          for (int v = 0; v < V; ++v) {
+            gv[v] = ns[v] ? __fdividef(gv[v], sRowK[s]) : 0.f;
+            one[v] = ns[v] ? 1.f : 0.f;
+          }
+          sts_v<V>(myR + s * PITCH, gv);
+          sts_v<V>(myE + s * PITCH, one);
+        }
+        if (c >= 0 && dleaf && any && active) {
+          float* dst = dleaf + (size_t)c * A * stride;
+          for (int t = 0; t < A; ++t) {
+            float out[V];
+            ld_f<V>(dst + t * stride, out);  // lanes with a state keep what phase 0 stored
 #pragma unroll
             for (int v = 0; v < V; ++v) {
-              z[v] = fmaf(k4.x, e[t][v], z[v]);
-              z[v] = fmaf(k4.y, e[t + 1][v], z[v]);
-              z[v] = fmaf(k4.z, e[t + 2][v], z[v]);
-              z[v] = fmaf(k4.w, e[t + 3][v], z[v]);
+              if (!ns[v]) continue;
+              float a = 0.f;
+              for (int s = 0; s < A; ++s) a = fmaf(sKt[t * AP + s], myR[s * PITCH + v], a);
+              out[v] = a;
             }
+            st_f<V>(dst + t * stride, out);
           }
-        } else {
-#pragma unroll
-          for (int t = 0; t < AP; ++t)
-#pragma unroll
-            for (int v = 0; v < V; ++v) z[v] = fmaf(krow[t], e[t][v], z[v]);
         }
+      } else {
+        // ---- child with a cost row (internal node or soft leaf) ---------------------------------
+        const int slot = ph - 3;
+        if (!(slot ? gen1 : gen0)) continue;
+        const int c = slot ? cc1 : cc0;
+        const float* src;
+        float* dst;
+        if (c >= p.n_leaves) {
+          src = dp + (size_t)(c - p.n_leaves) * A * stride;
+          dst = gbar + (size_t)(c - p.n_leaves) * A * stride;
+        } else {
+          src = p.leaf_cost + (size_t)c * A * stride + site0;
+          dst = dleaf ? dleaf + (size_t)c * A * stride : nullptr;
+        }
+        float e[AP][V];
 #pragma unroll
-        for (int v = 0; v < V; ++v) gv[v] = ok[v] ? __fdividef(gv[v], z[v]) : 0.f;
-        sts_v<V>(myR + s * PITCH, gv);
-      }
-      // gbar[child][t] = e[t] * sum_s K[s,t] r[s]; r comes back from this lane's own column
-      {
-        float r[AP][V];
-#pragma unroll
-        for (int s = 0; s < AP; ++s) {
-          if (s < A) ld_f<V>(myR + s * PITCH, r[s]);
+        for (int t = 0; t < AP; ++t) {
+          if (t < A) ld_f_stream<V>(src + t * stride, e[t]);
           else {
 #pragma unroll
-            for (int v = 0; v < V; ++v) r[s][v] = 0.f;
+            for (int v = 0; v < V; ++v) e[t][v] = INFINITY;
           }
         }
-#pragma unroll 4
-        for (int t = 0; t < A; ++t) {
-          float a[V], et[V];
+        // cotangent rows go straight to this lane's column of R (zero-filled past the end)
+        for (int s = 0; s < A; ++s) cp_async_v<V>(myR + s * PITCH, grow + s * stride, ok_bytes);
 #pragma unroll
-          for (int v = 0; v < V; ++v) a[v] = 0.f;
-          ld_f<V>(myE + t * PITCH, et);
-          const float* ktrow = sKt + t * AP;
-          if constexpr (AP % 4 == 0) {
+        for (int v = 0; v < V; ++v) {
+          float mm = e[0][v];
 #pragma unroll
-            for (int s = 0; s < AP; s += 4) {
-              const float4 k4 = *reinterpret_cast<const float4*>(ktrow + s);
+          for (int t = 1; t < AP; ++t) mm = fminf(mm, e[t][v]);
+#pragma unroll
+          for (int t = 0; t < AP; ++t) e[t][v] = ok[v] ? ex2_fast((mm - e[t][v]) * c1) : 0.f;
+        }
+#pragma unroll
+        for (int t = 0; t < AP; ++t) sts_v<V>(myE + t * PITCH, e[t]);
+        cp_async_wait_all();
+        // r[s] = g[s] / Z[s], four rows of K at a time (8 independent FFMA chains at V = 2)
+#pragma unroll 1
+        for (int sb = 0; sb < AP; sb += 4) {
+          float z[4][V];
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int v = 0; v < V; ++v) z[r][v] = 0.f;
+          const float* krow = sK + sb * AP;
+#pragma unroll
+          for (int t = 0; t < AP; t += 4) {
+            float4 k4[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) k4[r] = *reinterpret_cast<const float4*>(krow + r * AP + t);
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
 #pragma unroll
               for (int v = 0; v < V; ++v) {
-                a[v] = fmaf(k4.x, r[s][v], a[v]);
-                a[v] = fmaf(k4.y, r[s + 1][v], a[v]);
-                a[v] = fmaf(k4.z, r[s + 2][v], a[v]);
-                a[v] = fmaf(k4.w, r[s + 3][v], a[v]);
+                z[r][v] = fmaf(k4[r].x, e[t][v], z[r][v]);
+                z[r][v] = fmaf(k4[r].y, e[t + 1][v], z[r][v]);
+                z[r][v] = fmaf(k4[r].z, e[t + 2][v], z[r][v]);
+                z[r][v] = fmaf(k4[r].w, e[t + 3][v], z[r][v]);
               }
-            }
-          } else {
-#pragma unroll
-            for (int s = 0; s < AP; ++s)
-#pragma unroll
-              for (int v = 0; v < V; ++v) a[v] = fmaf(ktrow[s], r[s][v], a[v]);
           }
 #pragma unroll
-          for (int v = 0; v < V; ++v) a[v] *= et[v];
-          if (dst && active) st_f<V>(dst + (size_t)t * p.stride, a);
+          for (int r = 0; r < 4; ++r) {
+            float gv[V];
+            ld_f<V>(myR + (sb + r) * PITCH, gv);
+#pragma unroll
+            for (int v = 0; v < V; ++v) gv[v] *= rcp_fast(fmaxf(z[r][v], 1e-37f));
+            sts_v<V>(myR + (sb + r) * PITCH, gv);
+          }
+        }
+        // gbar[child][t] = e[t] * sum_s K[s,t] r[s]; r comes back from this lane's own column
+        {
+          float r[AP][V];
+#pragma unroll
+          for (int s = 0; s < AP; ++s) ld_f<V>(myR + s * PITCH, r[s]);
+#pragma unroll 1
+          for (int tb = 0; tb < AP; tb += 4) {
+            float a[4][V];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+#pragma unroll
+              for (int v = 0; v < V; ++v) a[q][v] = 0.f;
+            const float* ktrow = sKt + tb * AP;
+#pragma unroll
+            for (int s = 0; s < AP; s += 4) {
+              float4 k4[4];
+#pragma unroll
+              for (int q = 0; q < 4; ++q) k4[q] = *reinterpret_cast<const float4*>(ktrow + q * AP + s);
+#pragma unroll
+              for (int q = 0; q < 4; ++q)
+#pragma unroll
+                for (int v = 0; v < V; ++v) {
+                  a[q][v] = fmaf(k4[q].x, r[s][v], a[q][v]);
+                  a[q][v] = fmaf(k4[q].y, r[s + 1][v], a[q][v]);
+                  a[q][v] = fmaf(k4[q].z, r[s + 2][v], a[q][v]);
+                  a[q][v] = fmaf(k4[q].w, r[s + 3][v], a[q][v]);
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              float et[V];
+              ld_f<V>(myE + (tb + q) * PITCH, et);
+#pragma unroll
+              for (int v = 0; v < V; ++v) a[q][v] *= et[v];
+              if (dst && active && tb + q < A) st_f<V>(dst + (size_t)(tb + q) * stride, a[q]);
+            }
+          }
         }
       }
       if constexpr (WANT_DC) {
+        // dC outer product over this warp's sites: lane = (pair tile, site group)
         __syncwarp();
-        sweep(acc);
+        float tmp[RS][CS];
+#pragma unroll
+        for (int a = 0; a < RS; ++a)
+#pragma unroll
+          for (int b = 0; b < CS; ++b) tmp[a][b] = 0.f;
+#pragma unroll 2
+        for (int it = 0; it < Cfg::NCH; ++it) {
+          float4 rr[RS], ee[CS];
+#pragma unroll
+          for (int a = 0; a < RS; ++a) rr[a] = *reinterpret_cast<const float4*>(rbase + a * PITCH + it * (SG * 4));
+#pragma unroll
+          for (int b = 0; b < CS; ++b) ee[b] = *reinterpret_cast<const float4*>(ebase + b * PITCH + it * (SG * 4));
+#pragma unroll
+          for (int a = 0; a < RS; ++a)
+#pragma unroll
+            for (int b = 0; b < CS; ++b) {
+              float x = tmp[a][b];
+              x = fmaf(rr[a].x, ee[b].x, x);
+              x = fmaf(rr[a].y, ee[b].y, x);
+              x = fmaf(rr[a].z, ee[b].z, x);
+              x = fmaf(rr[a].w, ee[b].w, x);
+              tmp[a][b] = x;
+            }
+        }
+        if (gspace) {
+#pragma unroll
+          for (int a = 0; a < RS; ++a)
+#pragma unroll
+            for (int b = 0; b < CS; ++b) accG[a][b] += tmp[a][b];
+        } else {
+#pragma unroll
+          for (int a = 0; a < RS; ++a)
+#pragma unroll
+            for (int b = 0; b < CS; ++b) acc[a][b] += tmp[a][b];
+        }
         __syncwarp();
-      }
-    }
-    if constexpr (WANT_DC) {
-      if (++since_flush == kFlush) {
-        since_flush = 0;
-        flush(acc, true);
-        flush(accG, false);
       }
     }
   }
   if constexpr (WANT_DC) {
-    flush(acc, true);
-    flush(accG, false);
     __syncwarp();
     for (int i = lane; i < A * A; i += 32) {
       const double v = sAcc[(i / A) * AP + i % A];
