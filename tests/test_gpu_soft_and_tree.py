@@ -159,3 +159,35 @@ def test_tree_cost_autograd_matches_reference_signatures():
   assert _relerr(At.grad.cpu().numpy(), 3.0 * dA64) <= RTOL
   c2 = compute_soft_cost(St.detach(), At.detach(), torch.eye(4, device="cuda"))
   assert abs(float(c2) - float(c)) <= RTOL * abs(float(c))
+
+
+TC_CASES = [(5, 7, 3), (127, 1000, 4), (128, 40, 20), (129, 33, 5), (200, 150, 20), (256, 64, 4), (257, 20, 4)]
+
+
+@pytest.mark.parametrize("N,L,Q", TC_CASES)
+def test_tree_cost_tcgen05_and_simt_paths_agree_with_oracle(N, L, Q, monkeypatch):
+  """Identity cost, N <= 256 runs on tcgen05 (3xTF32); TREX_TREE_COST_PATH=simt pins the exact-f32
+  CUDA-core path; N = 257 falls back to it.  Both must meet the 1e-5 bar against float64
+  (tree.py:163-209) and agree with each other."""
+  import torch
+  from trex_b200.tree import tree_cost_value_and_grad
+
+  S, adj, _ = _tree_inputs(N, L, Q, seed=3 * N + L + Q, adj_kind="bernoulli")
+  want, dS64, dA64, _ = to.soft_cost_value_and_grad(S, adj, None)
+  _, (t1, t2, t3) = to.compute_soft_cost(S, adj, None, dtype=np.float64)
+  bound = RTOL * abs(want) + 4 * np.finfo(np.float32).eps * (abs(t1) + abs(t2) + abs(t3))
+  St, At = torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda()
+  got = {}
+  for path in ("auto", "simt"):
+    monkeypatch.setenv("TREX_TREE_COST_PATH", path)
+    cost, dS, dA, _ = tree_cost_value_and_grad(St, At, None)
+    torch.cuda.synchronize()
+    assert abs(float(cost) - want) <= bound, path
+    assert _relerr(dS.cpu().numpy(), dS64) <= RTOL, path
+    assert _relerr(dA.cpu().numpy(), dA64) <= RTOL, path
+    got[path] = (float(cost), dS.cpu().numpy(), dA.cpu().numpy())
+  assert abs(got["auto"][0] - got["simt"][0]) <= 2 * bound
+  # value only (no gradients requested)
+  monkeypatch.setenv("TREX_TREE_COST_PATH", "auto")
+  cost, dS, dA, _ = tree_cost_value_and_grad(St, At, None, want_dseq=False, want_dadj=False)
+  assert dS is None and dA is None and abs(float(cost) - want) <= bound

@@ -13,6 +13,7 @@
 // axis K = L*Q, f64 cross-CTA accumulation of G).  It is the parity baseline for the tcgen05
 // path and the fallback for shapes the tensor-core kernel does not take.
 #include "common.cuh"
+#include "tree_cost_tc.cuh"
 
 namespace trex {
 
@@ -265,11 +266,12 @@ extern "C" {
 
 size_t trex_tree_cost_workspace_bytes(int n_nodes, int64_t k, int n_states) {
   using namespace trex;
-  (void)k;
   if (n_nodes < 1 || n_states < 1) return 0;
-  return tc_align(sizeof(double) * (size_t)n_nodes * n_nodes) +
+  const size_t tcb = n_nodes <= tc::kMaxNodes ? tc::workspace_bytes(n_nodes, k) : 0;  // tcgen05 path (either path may run)
+  const size_t simt = tc_align(sizeof(double) * (size_t)n_nodes * n_nodes) +
          tc_align(sizeof(double) * (size_t)n_states * n_states) + 512 +
          tc_align(sizeof(float) * (size_t)n_nodes);
+  return simt > tcb ? simt : tcb;
 }
 
 int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cost, int cost_kind,
@@ -285,6 +287,8 @@ int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cos
   const int N = n_nodes, Q = n_states;
   const long long K = (long long)n_sites * Q;
   cudaStream_t s = (cudaStream_t)stream;
+  // identity cost, N <= 256: tcgen05 / TMEM / TMA path (3xTF32); everything else: exact-f32 CUDA cores
+  if (tc::supported(N, cost_kind)) return tc::run(seqs, adj, N, K, out_cost, d_seqs, d_adj, workspace, s);
   TcWorkspace w = tc_carve(workspace, N, Q);
   tc_prologue_kernel<<<N, 128, 0, s>>>(adj, N, Q, w);
   TREX_CHECK_LAUNCH("tc_prologue_kernel");

@@ -1,0 +1,510 @@
+// Soft-adjacency tree cost on the 5th-gen tensor cores (tcgen05 + TMEM + TMA), identity cost.
+//
+// Replaces compute_surrogate_cost / compute_soft_cost(cost_matrix=None)
+// (src/trex/tree.py:163-209, 212-266 with W = S) and their reverse mode
+// (jax.value_and_grad in src/trex/evals/benchmark.py:167-173).  With
+//     M = diag((rowsum+colsum)/2) - Adj,   G = S S^T  (N x N, contraction over K = L*Q):
+//     cost = <M, G>,   dAdj_ij = (G_ii + G_jj)/2 - G_ij,   dS = (M + M^T) S.
+// Both contractions run as tcgen05.mma kind::tf32 with fp32 accumulators in TMEM.  A single
+// tf32 pass (10-bit mantissa) misses the 1e-5 bar, so every operand is split
+// x = hi + lo (hi = x with the low 13 mantissa bits cleared, lo = x - hi, both exact) and each
+// product is evaluated as hi*hi + hi*lo + lo*hi into the same accumulator (3xTF32).
+//
+//   prep kernel : d, M + M^T (hi/lo), S -> S_hi/S_lo [Npad][Kp] and transposed ST_hi/ST_lo [Kp][Npad]
+//   gemm kernel : CTA role by blockIdx —
+//                 gram CTAs: split-K slice of G = S S^T  -> G by 128-bit red.global.add.v4.f32
+//                 dS   CTAs: 128 columns of dS^T = ST (M + M^T)  -> dS (coalesced along K)
+//                 TMA (128B swizzle) -> 2..3-stage mbarrier ring -> single-thread tcgen05.mma ->
+//                 tcgen05.commit -> all four warps read TMEM with tcgen05.ld
+//   final kernel: cost = <M, G>, dAdj.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "tree_cost_tc.cuh"
+
+namespace trex {
+namespace tc {
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra.uni WAIT_DONE;\n"
+      "bra.uni WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c_inner, int c_outer) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c_inner), "r"(c_outer)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_out, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_out)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem]^T, kind::tf32, issued by ONE thread for the CTA
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrives when all previously issued MMAs of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 lanes x 32 consecutive columns -> 32 registers per thread
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+      "tcgen05.wait::ld.sync.aligned;\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major operand tile in shared memory, rows of 128 bytes (32 tf32), 128B swizzle as written by
+// TMA: 8-row groups are 1024 bytes apart (SBO); descriptor version 1 (Blackwell).
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);  // start address
+  d |= (uint64_t)1 << 16;                      // LBO (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;            // SBO
+  d |= (uint64_t)1 << 46;                      // version
+  d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
+  return d;
+}
+// kind::tf32, fp32 accumulate, both operands K-major
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
+// ---------------------------------------------------------------------------------------------
+// prep kernel
+// ---------------------------------------------------------------------------------------------
+// grid.x = Npad (rows of M + M^T, d, zeroing) + transpose tiles; block = 256
+__global__ void __launch_bounds__(256)
+    prep_kernel(const float* __restrict__ S, const float* __restrict__ adj, int N, long long K, TcBuffers w) {
+  const int tid = threadIdx.x;
+  const int npad = w.npad;
+  if ((int)blockIdx.x < npad) {
+    // ---- row i of Msym = M + M^T (hi/lo), d_i ------------------------------------------------
+    const int i = blockIdx.x;
+    __shared__ float red[8];
+    __shared__ float s_d;
+    float acc = 0.f;
+    if (i < N)
+      for (int j = tid; j < N; j += 256) acc += adj[(size_t)i * N + j] + adj[(size_t)j * N + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((tid & 31) == 0) red[tid >> 5] = acc;
+    __syncthreads();
+    if (tid == 0) {
+      float t = 0.f;
+      for (int q = 0; q < 8; ++q) t += red[q];
+      s_d = 0.5f * t;
+      if (i < N) w.d[i] = s_d;
+    }
+    __syncthreads();
+    for (int j = tid; j < npad; j += 256) {
+      float m = 0.f;
+      if (i < N && j < N) m = (i == j ? 2.f * s_d : 0.f) - adj[(size_t)i * N + j] - adj[(size_t)j * N + i];
+      const float hi = tf32_hi(m);
+      w.m_hi[(size_t)i * npad + j] = hi;
+      w.m_lo[(size_t)i * npad + j] = m - hi;
+      w.g[(size_t)i * npad + j] = 0.f;
+    }
+    if (i == 0 && tid == 0) { *w.cost = 0.0; *w.ticket = 0u; }
+    return;
+  }
+  // ---- S -> S_hi/S_lo [npad][Kp] and ST_hi/ST_lo [Kp][npad]: 32 x 32 tiles through smem ----------
+  __shared__ float t_hi[32][33], t_lo[32][33];
+  const long long tile = (long long)blockIdx.x - npad;
+  const int row_tiles = npad / 32;
+  const long long kt = tile / row_tiles;
+  const int rt = (int)(tile % row_tiles);
+  const int tx = tid & 31, ty = tid >> 5;  // 32 x 8
+  for (int r = ty; r < 32; r += 8) {
+    const int row = rt * 32 + r;
+    const long long col = kt * 32 + tx;
+    float x = 0.f;
+    if (row < N && col < K) x = S[(size_t)row * K + col];
+    const float hi = tf32_hi(x), lo = x - hi;
+    w.s_hi[(size_t)row * w.kp + col] = hi;
+    w.s_lo[(size_t)row * w.kp + col] = lo;
+    t_hi[r][tx] = hi;
+    t_lo[r][tx] = lo;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const long long col = kt * 32 + r;  // row of ST
+    const int row = rt * 32 + tx;       // column of ST
+    w.st_hi[(size_t)col * npad + row] = t_hi[tx][r];
+    w.st_lo[(size_t)col * npad + row] = t_lo[tx][r];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// tcgen05 GEMM kernel: gram CTAs (split-K of G = S S^T) and dS CTAs (dS^T = ST (M + M^T))
+// ---------------------------------------------------------------------------------------------
+template <int NPAD>
+struct GemmCfg {
+  static constexpr int MBLK = NPAD / 128;                         // M blocks of the gram accumulator
+  static constexpr int BK = 32;                                   // tf32 per k-block = one 128 B swizzle row
+  static constexpr int A_BYTES = 128 * 128;                       // 128 rows x 128 B (dS role only)
+  static constexpr int B_BYTES = NPAD * 128;
+  static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // A_hi, A_lo, B_hi, B_lo
+  static constexpr int STAGES = NPAD == 128 ? 3 : 2;
+  static constexpr int TMEM_COLS = NPAD;                          // one 128 x NPAD fp32 accumulator
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+struct GemmParams {
+  int n_nodes;
+  long long k;          // true contraction length (columns of S)
+  int n_gram;           // gram CTAs = slabs
+  int kb_per_gram;      // k-blocks per gram CTA
+  int n_kb;             // ceil(k / 32)
+  int n_ds;             // dS CTAs = ceil(k / 128), 0 when d_seqs is not wanted
+  float* g;             // [NPAD][NPAD] G = S S^T, zeroed by the prep kernel
+  float* d_seqs;        // [N][K]
+};
+
+template <int NPAD>
+__global__ void __launch_bounds__(128, 1)
+    tc_gemm_kernel(const __grid_constant__ CUtensorMap map_s_hi, const __grid_constant__ CUtensorMap map_s_lo,
+                   const __grid_constant__ CUtensorMap map_st_hi, const __grid_constant__ CUtensorMap map_st_lo,
+                   const __grid_constant__ CUtensorMap map_m_hi, const __grid_constant__ CUtensorMap map_m_lo,
+                   const GemmParams p) {
+  using Cfg = GemmCfg<NPAD>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + Cfg::STAGES * Cfg::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool is_gram = (int)blockIdx.x < p.n_gram * Cfg::MBLK;   // gram unit = (slab, M block)
+  const int unit = is_gram ? blockIdx.x / Cfg::MBLK : blockIdx.x - p.n_gram * Cfg::MBLK;
+  const int mblk = is_gram ? blockIdx.x % Cfg::MBLK : 0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(is_gram ? &map_s_hi : &map_st_hi);
+    prefetch_tmap(is_gram ? &map_s_lo : &map_st_lo);
+    if (!is_gram) { prefetch_tmap(&map_m_hi); prefetch_tmap(&map_m_lo); }
+    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, Cfg::TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  int it0, it1;  // k-block range (gram) / j-block range (dS)
+  if (is_gram) {
+    it0 = unit * p.kb_per_gram;
+    it1 = min(p.n_kb, it0 + p.kb_per_gram);
+  } else {
+    it0 = 0;
+    it1 = NPAD / Cfg::BK;
+  }
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = it0; it < it1; ++it) {
+      mbar_wait(empty_bar + stage, phase ^ 1);
+      uint8_t* st = tiles + stage * Cfg::STAGE_BYTES;
+      if (is_gram) {
+        mbar_expect_tx(full_bar + stage, 2 * Cfg::B_BYTES);
+        tma_load_2d(st + 2 * Cfg::A_BYTES, &map_s_hi, full_bar + stage, it * Cfg::BK, 0);
+        tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &map_s_lo, full_bar + stage, it * Cfg::BK, 0);
+      } else {
+        mbar_expect_tx(full_bar + stage, 2 * Cfg::A_BYTES + 2 * Cfg::B_BYTES);
+        tma_load_2d(st, &map_st_hi, full_bar + stage, it * Cfg::BK, unit * 128);
+        tma_load_2d(st + Cfg::A_BYTES, &map_st_lo, full_bar + stage, it * Cfg::BK, unit * 128);
+        tma_load_2d(st + 2 * Cfg::A_BYTES, &map_m_hi, full_bar + stage, it * Cfg::BK, 0);
+        tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &map_m_lo, full_bar + stage, it * Cfg::BK, 0);
+      }
+      if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer (one thread) =====
+    constexpr uint32_t idesc = make_idesc_tf32(128, NPAD);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = it0; it < it1; ++it) {
+      mbar_wait(full_bar + stage, phase);
+      tc_fence_after();
+      const uint32_t st = smem_u32(tiles + stage * Cfg::STAGE_BYTES);
+      const uint32_t b_hi = st + 2 * Cfg::A_BYTES, b_lo = b_hi + Cfg::B_BYTES;
+      {
+        const uint32_t a_hi = is_gram ? b_hi + mblk * Cfg::A_BYTES : st;
+        const uint32_t a_lo = is_gram ? b_lo + mblk * Cfg::A_BYTES : st + Cfg::A_BYTES;
+        const uint32_t d_tmem = tmem_base;
+#pragma unroll
+        for (int k4 = 0; k4 < Cfg::BK / 8; ++k4) {
+          const uint64_t adh = make_kmajor_sw128_desc(a_hi) + 2 * k4, adl = make_kmajor_sw128_desc(a_lo) + 2 * k4;
+          const uint64_t bdh = make_kmajor_sw128_desc(b_hi) + 2 * k4, bdl = make_kmajor_sw128_desc(b_lo) + 2 * k4;
+          umma_tf32(d_tmem, adh, bdh, idesc, (it > it0 || k4 > 0) ? 1u : 0u);
+          umma_tf32(d_tmem, adh, bdl, idesc, 1u);
+          umma_tf32(d_tmem, adl, bdh, idesc, 1u);
+        }
+      }
+      umma_commit(empty_bar + stage);  // frees the smem slot once these MMAs have read it
+      if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+    }
+    umma_commit(tmem_full_bar);
+  }
+  __syncwarp();
+
+  // ===== epilogue: all four warps, warp w owns TMEM lanes 32w .. 32w+31 =====
+  mbar_wait(tmem_full_bar, 0);
+  tc_fence_after();
+  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+  if (is_gram) {
+    // partial G of this split-K slice -> G with 128-bit fire-and-forget reductions (no slabs)
+    {
+      float* row = p.g + (size_t)(mblk * 128 + warp * 32 + lane) * NPAD;
+#pragma unroll 1
+      for (int c0 = 0; c0 < NPAD; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_base + lane_base + c0, v);
+#pragma unroll
+        for (int q = 0; q < 32; q += 4)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(row + c0 + q), "f"(v[q]), "f"(v[q + 1]),
+                       "f"(v[q + 2]), "f"(v[q + 3])
+                       : "memory");
+      }
+    }
+  } else {
+    const long long kcol = (long long)unit * 128 + warp * 32 + lane;
+#pragma unroll 1
+    for (int c0 = 0; c0 < NPAD; c0 += 32) {
+      float v[32];
+      tmem_ld32(tmem_base + lane_base + c0, v);
+      if (kcol < p.k) {
+#pragma unroll
+        for (int q = 0; q < 32; ++q)
+          if (c0 + q < p.n_nodes) p.d_seqs[(size_t)(c0 + q) * p.k + kcol] = v[q];
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------
+// final kernel: cost = <M, G>, dAdj_ij = (G_ii + G_jj)/2 - G_ij.  Block = row i.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    final_kernel(const float* __restrict__ adj, int N, TcBuffers w, float* __restrict__ out_cost,
+                 float* __restrict__ d_adj) {
+  __shared__ float diag[kMaxNodes];
+  const int i = blockIdx.x, tid = threadIdx.x;
+  const int npad = w.npad;
+  for (int j = tid; j < N; j += 256) diag[j] = w.g[(size_t)j * npad + j];
+  __syncthreads();
+  double part = 0.0;
+  for (int j = tid; j < N; j += 256) {
+    const float g = w.g[(size_t)i * npad + j];
+    const float a = adj[(size_t)i * N + j];
+    const double m = (i == j ? (double)w.d[i] : 0.0) - (double)a;
+    part += m * (double)g;
+    if (d_adj) d_adj[(size_t)i * N + j] = 0.5f * (diag[i] + diag[j]) - g;
+  }
+  block_atomic_add(part, w.cost);
+  __shared__ bool last;
+  __threadfence();
+  if (tid == 0) last = (atomicAdd(w.ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (last && tid == 0) {
+    __threadfence();
+    *out_cost = (float)(*(volatile double*)w.cost);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static int pad_nodes(int n) { return n <= 128 ? 128 : 256; }
+static long long pad_k(long long k) { return (k + 127) / 128 * 128; }
+
+static void plan_split(long long k, int& n_kb, int& kb_per, int& n_gram) {
+  n_kb = (int)((k + 31) / 32);
+  kb_per = (n_kb + kMaxSlabs - 1) / kMaxSlabs;
+  if (kb_per < 4) kb_per = 4;
+  n_gram = (n_kb + kb_per - 1) / kb_per;
+}
+
+static TcBuffers carve(void* ws, int n_nodes, long long k) {
+  TcBuffers w{};
+  w.npad = pad_nodes(n_nodes);
+  w.kp = pad_k(k);
+  int n_kb, kb_per;
+  plan_split(k, n_kb, kb_per, w.n_slabs);
+  char* p = (char*)ws;
+  auto take = [&](size_t bytes) { char* r = p; p += align256(bytes); return r; };
+  w.cost = (double*)take(8);
+  w.ticket = (unsigned*)take(4);
+  w.d = (float*)take(sizeof(float) * kMaxNodes);
+  const size_t nn = sizeof(float) * (size_t)w.npad * w.npad, nk = sizeof(float) * (size_t)w.npad * w.kp;
+  w.m_hi = (float*)take(nn);
+  w.m_lo = (float*)take(nn);
+  w.s_hi = (float*)take(nk);
+  w.s_lo = (float*)take(nk);
+  w.st_hi = (float*)take(nk);
+  w.st_lo = (float*)take(nk);
+  w.g = (float*)take(nn);
+  return w;
+}
+
+size_t workspace_bytes(int n_nodes, long long k) {
+  if (n_nodes < 1 || n_nodes > kMaxNodes || k < 1) return 0;
+  const int npad = pad_nodes(n_nodes);
+  const long long kp = pad_k(k);
+  int n_kb, kb_per, n_gram;
+  plan_split(k, n_kb, kb_per, n_gram);
+  const size_t nn = align256(sizeof(float) * (size_t)npad * npad), nk = align256(sizeof(float) * (size_t)npad * kp);
+  (void)n_gram;
+  return 256 * 2 + align256(sizeof(float) * kMaxNodes) + 3 * nn + 4 * nk + 256;
+}
+
+bool supported(int n_nodes, int cost_kind) {
+  // TREX_TREE_COST_PATH=simt keeps the exact-f32 CUDA-core path (parity baseline); read per call so
+  // tests can exercise both paths in one process
+  const char* e = getenv("TREX_TREE_COST_PATH");
+  const bool forced_simt = e && e[0] == 's';
+  return !forced_simt && cost_kind == 0 && n_nodes >= 1 && n_nodes <= kMaxNodes;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// row-major f32 [rows][cols] with `pitch` floats per row; box = box_rows x 32 floats, 128B swizzle
+static int make_map(CUtensorMap* map, float* base, long long rows, long long cols, long long pitch, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("tree_cost(tcgen05): cuTensorMapEncodeTiled is not available from the driver");
+    return TREX_ERR_CUDA;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(float)};
+  cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("tree_cost(tcgen05): cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return TREX_ERR_CUDA;
+  }
+  return TREX_OK;
+}
+
+template <int NPAD>
+static int launch_gemm(const TcBuffers& w, const GemmParams& gp, cudaStream_t stream) {
+  CUtensorMap ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo;
+  int rc;
+  if ((rc = make_map(&ms_hi, w.s_hi, NPAD, w.kp, w.kp, NPAD))) return rc;
+  if ((rc = make_map(&ms_lo, w.s_lo, NPAD, w.kp, w.kp, NPAD))) return rc;
+  if ((rc = make_map(&mst_hi, w.st_hi, w.kp, NPAD, NPAD, 128))) return rc;
+  if ((rc = make_map(&mst_lo, w.st_lo, w.kp, NPAD, NPAD, 128))) return rc;
+  if ((rc = make_map(&mm_hi, w.m_hi, NPAD, NPAD, NPAD, NPAD))) return rc;
+  if ((rc = make_map(&mm_lo, w.m_lo, NPAD, NPAD, NPAD, NPAD))) return rc;
+  auto kern = tc_gemm_kernel<NPAD>;
+  rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<NPAD>::SMEM_BYTES),
+                  "cudaFuncSetAttribute(tc_gemm_kernel)");
+  if (rc) return rc;
+  kern<<<gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds, 128, GemmCfg<NPAD>::SMEM_BYTES, stream>>>(ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo, gp);
+  return check_cuda(cudaPeekAtLastError(), "tc_gemm_kernel");
+}
+
+int run(const float* seqs, const float* adj, int n_nodes, long long k, float* out_cost, float* d_seqs, float* d_adj,
+        void* workspace, cudaStream_t stream) {
+  TcBuffers w = carve(workspace, n_nodes, k);
+  const long long tiles = (long long)(w.npad / 32) * (w.kp / 32);
+  TREX_CHECK_ARG(w.npad + tiles <= 2147483647LL, "tree_cost(tcgen05): K too large");
+  prep_kernel<<<(unsigned)(w.npad + tiles), 256, 0, stream>>>(seqs, adj, n_nodes, k, w);
+  TREX_CHECK_LAUNCH("tc::prep_kernel");
+  GemmParams gp{};
+  gp.n_nodes = n_nodes;
+  gp.k = k;
+  plan_split(k, gp.n_kb, gp.kb_per_gram, gp.n_gram);
+  gp.n_ds = d_seqs ? (int)((k + 127) / 128) : 0;
+  gp.g = w.g;
+  gp.d_seqs = d_seqs;
+  int rc = w.npad == 128 ? launch_gemm<128>(w, gp, stream) : launch_gemm<256>(w, gp, stream);
+  if (rc) return rc;
+  final_kernel<<<n_nodes, 256, 0, stream>>>(adj, n_nodes, w, out_cost, d_adj);
+  TREX_CHECK_LAUNCH("tc::final_kernel");
+  return TREX_OK;
+}
+
+}  // namespace tc
+}  // namespace trex
