@@ -183,42 +183,81 @@ def workload_config(args, sites_per_rank):
 
 
 def tree_cost_bench(torch, iters=200):
-  """BASELINE config c2: soft-topology tree_cost + grad, 64 taxa (127 nodes) x 1k sites, DNA."""
+  """BASELINE config c2: soft-topology tree_cost + grad, 64 taxa (127 nodes) x 1k sites, DNA, and the
+  largest shape of the reference's own script (benchmark_tree_cost.py:41-43: N=200, L=1000, Q=20).
+  Identity cost -> tcgen05 path.  Timed twice: replayed from a CUDA graph (device-bound) and
+  dispatched call by call from Python through ctypes (what an eager caller sees)."""
   from oracle import tree_oracle as to
   from trex_b200 import _lib
   from trex_b200.tree import tree_cost_value_and_grad
 
-  rng = np.random.default_rng(2)
-  N, L, Q, n = 127, 1000, 4, 64
-  S = to.softmax(rng.normal(size=(N, L, Q))).astype(np.float32)
-  S[:n] = np.eye(Q, dtype=np.float32)[rng.integers(0, Q, size=(n, L))]
-  adj = to.update_tree(rng.normal(size=(N - 1, N - n)).astype(np.float32),
-                       np.zeros((N - 1, N - n), np.float32)).astype(np.float32)
-  St, At = torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda()
-  ws = torch.empty(_lib.load().trex_tree_cost_workspace_bytes(N, L * Q, Q), dtype=torch.uint8, device="cuda")
-  out = {"cost": torch.empty((), device="cuda"), "dS": torch.empty_like(St), "dA": torch.empty_like(At)}
-  for _ in range(10):
-    tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
-  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-  torch.cuda.synchronize()
-  e0.record()
-  for _ in range(iters):
-    tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
-  e1.record()
-  torch.cuda.synchronize()
-  ms = e0.elapsed_time(e1) / iters
-  # CPU: NumPy (BLAS) restatement of the same value+grad, float32 like the reference
-  t0 = time.perf_counter()
-  reps = 5
-  for _ in range(reps):
-    to.soft_cost_value_and_grad(S, adj, None, dtype=np.float32)
-  cpu_ms = (time.perf_counter() - t0) / reps * 1e3
-  return {"metric": "tree_cost_grad_steps_per_s", "value": 1e3 / ms, "unit": "grad steps/s", "ms_per_step": ms,
-          "config": "c2: 127 nodes x 1000 sites x 4 states, identity cost, value + dS + dAdj",
-          "flop_per_step": 4 * N * N * L * Q, "bytes_per_step": 4 * N * L * Q * 2 + 8 * N * N,
-          "note": "launch/latency bound at this size (SURVEY H7)",
-          "cpu_baseline": {"value": 1e3 / cpu_ms, "unit": "grad steps/s", "kind": "port",
-                           "sample": "NumPy/BLAS float32 restatement of tree.py value+grad"}}
+  def one(N, L, Q, n, seed, softmax_adj):
+    rng = np.random.default_rng(seed)
+    S = to.softmax(rng.normal(size=(N, L, Q))).astype(np.float32)
+    if n:
+      S[:n] = np.eye(Q, dtype=np.float32)[rng.integers(0, Q, size=(n, L))]
+    if softmax_adj:
+      adj = to.update_tree(rng.normal(size=(N - 1, N - n)).astype(np.float32),
+                           np.zeros((N - 1, N - n), np.float32)).astype(np.float32)
+    else:
+      adj = (rng.random((N, N)) < 0.1).astype(np.float32)  # benchmark_tree_cost.py:57
+    St, At = torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda()
+    ws = torch.empty(_lib.load().trex_tree_cost_workspace_bytes(N, L * Q, Q), dtype=torch.uint8, device="cuda")
+    out = {"cost": torch.empty((), device="cuda"), "dS": torch.empty_like(St), "dA": torch.empty_like(At)}
+    call = lambda: tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
+    for _ in range(10):
+      call()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+      call()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_eager = e0.elapsed_time(e1) / iters
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+      call()
+      stream.synchronize()
+      g = torch.cuda.CUDAGraph()
+      with torch.cuda.graph(g, stream=stream):
+        call()
+      g.replay()
+      stream.synchronize()
+      e0.record(stream)
+      for _ in range(iters):
+        g.replay()
+      e1.record(stream)
+      stream.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    t0 = time.perf_counter()
+    reps = 3
+    for _ in range(reps):
+      to.soft_cost_value_and_grad(S, adj, None, dtype=np.float32)
+    cpu_ms = (time.perf_counter() - t0) / reps * 1e3
+    flop = 4.0 * N * N * L * Q
+    return {"shape": f"{N} nodes x {L} sites x {Q} states, identity cost, value + dS + dAdj",
+            "ms_per_step": ms, "grad_steps_per_s": 1e3 / ms, "ms_per_step_eager_python": ms_eager,
+            "flop_per_step": flop, "useful_tflops": flop / ms / 1e9, "tf32x3_issued_tflops": 3 * flop / ms / 1e9,
+            "cpu_grad_steps_per_s": 1e3 / cpu_ms}
+
+  c2 = one(127, 1000, 4, 64, 2, True)
+  big = one(200, 1000, 20, 0, 242, False)
+  bf16 = None
+  pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+  if os.path.exists(pk):
+    with open(pk) as f:
+      bf16 = float(json.load(f).get("bf16_tflops", 0)) or None
+  tf32_peak = (bf16 or 1590.0) / 2  # no TF32 figure is measured on this pool; dense tf32 = bf16 / 2
+  return {"metric": "tree_cost_grad_steps_per_s", "value": c2["grad_steps_per_s"], "unit": "grad steps/s",
+          "ms_per_step": c2["ms_per_step"], "config": "c2: " + c2["shape"], "c2": c2, "script_n200": big,
+          "path": "tcgen05 kind::tf32, 3xTF32 split, TMA + TMEM (tree_cost_tc.cu); CUDA-graph replay",
+          "roofline": {"bound": "tensor", "achieved": big["tf32x3_issued_tflops"], "peak": tf32_peak,
+                       "unit": "TFLOP/s", "frac": big["tf32x3_issued_tflops"] / tf32_peak,
+                       "note": "issued tf32 flops (3 MMAs per product) at N=200, K=20000 over measured bf16 peak / 2; "
+                               "c2 itself is launch/latency bound (SURVEY H7)"},
+          "cpu_baseline": {"value": c2["cpu_grad_steps_per_s"], "unit": "grad steps/s", "kind": "port",
+                           "sample": "NumPy/BLAS float32 restatement of tree.py value+grad at c2"}}
 
 
 def run_gpu(args):
@@ -343,13 +382,17 @@ def run_gpu(args):
       gbs = per_site[nm] * L / (kern_ms[nm] * 1e-3) / 1e9
       roof_all[nm] = {"ms": kern_ms[nm], "alg_bytes": per_site[nm] * L, "achieved": gbs, "frac": gbs / peak}
     dom = max(["hard_fwd", "soft_fwd", "soft_bwd"], key=lambda k: kern_ms[k])
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
+    # (profiles/r01_*_ncu_full.txt), valid for the c5 shape at 100k sites per rank only
+    ncu_traffic = {"hard_fwd": 12.90e9, "soft_fwd": 8.76e9, "soft_bwd": 25.36e9}
+    traffic = ncu_traffic.get(dom) if (L == N_SITES) else None
     line = {
       "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
       "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
       "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
       "config": workload_config(args, L),
       "roofline": {"bound": "hbm", "kernel": dom, "achieved": roof_all[dom]["achieved"], "peak": peak,
-                   "peak_source": peak_src, "unit": "GB/s", "frac": roof_all[dom]["frac"], "traffic": None,
+                   "peak_source": peak_src, "unit": "GB/s", "frac": roof_all[dom]["frac"], "traffic": traffic,
                    "note": "achieved = SURVEY 8(d) algorithmic bytes / CUDA-event launch time on the launching stream"},
       "roofline_all": roof_all,
       "kernel_ms": kern_ms,
