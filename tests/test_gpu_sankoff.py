@@ -27,6 +27,8 @@ def _case(kind, n, A, L, seed, cost_kind="unit", rate=0.2):
   states = synth.evolve(par, L, A, rate, rng)
   if cost_kind == "unit":
     cost = synth.unit_cost(A)
+  elif cost_kind == "unit3":  # uniform off-diagonal cost != 1 (O(A) kernels, sankoff_uniform.cu)
+    cost = 3.0 * synth.unit_cost(A)
   elif cost_kind == "int":
     cost = synth.random_int_cost(A, 5, rng)
   else:  # non-integer, asymmetric: exercises the exact-f32 path
@@ -52,6 +54,10 @@ CASES = [
   ("random", 7, 3, 250, "float"),
   ("balanced", 32, 7, 40, "int"),
   ("random", 6, 24, 19, "int"),       # A in 21..32 -> padded AP=32 kernels
+  ("random", 6, 24, 19, "unit"),
+  ("cat", 21, 20, 70, "unit3"),
+  ("random", 40, 5, 200, "unit3"),
+  ("random", 33, 8, 129, "unit"),
 ]
 
 
@@ -61,7 +67,7 @@ def test_hard_forward_and_traceback_bit_exact(kind, n, A, L, ck, mode):
   torch = _torch()
   from trex_b200.sankoff import SankoffEngine
 
-  adj, cost, states, _ = _case(kind, n, A, L, seed=n * 131 + A * 7 + L)
+  adj, cost, states, _ = _case(kind, n, A, L, seed=n * 131 + A * 7 + L, cost_kind=ck)
   n_all = 2 * n - 1
   tabs = so.run_sankoff_tables(adj, cost, states[:n], n_all, A, n)
   eng = SankoffEngine(n_all, n, A, L)

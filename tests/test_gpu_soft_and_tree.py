@@ -25,7 +25,7 @@ def _soft_case(kind, n, A, L, seed, cost_kind):
     synth.caterpillar_parents(n) if kind == "cat" else synth.random_join_parents(n, rng))
   adj = synth.parents_to_adjacency(par)
   states = synth.evolve(par, L, A, 0.2, rng)
-  cost = synth.unit_cost(A) if cost_kind == "unit" else (
+  cost = synth.unit_cost(A) if cost_kind == "unit" else 2.5 * synth.unit_cost(A) if cost_kind == "unit2.5" else (
     synth.random_int_cost(A, 5, rng) if cost_kind == "int" else (rng.random((A, A)) * 2).astype(np.float32))
   return adj, cost, states
 
@@ -38,6 +38,11 @@ SOFT_CASES = [
   ("random", 14, 2, 300, "unit", 0.3),
   ("random", 8, 4, 50, "int", 0.01),   # max(C)/T > 80 -> direct (non exp-domain) evaluation
   ("random", 6, 24, 21, "unit", 0.7),  # padded AP=32 kernels
+  # uniform off-diagonal cost: the O(A) forward kernels of sankoff_uniform.cu
+  ("cat", 19, 20, 150, "unit", 1.0),
+  ("random", 37, 20, 70, "unit2.5", 0.6),
+  ("random", 23, 7, 130, "unit2.5", 2.0),
+  ("random", 9, 5, 40, "unit", 0.01),   # a/T > 80 -> general kernel, direct evaluation
 ]
 
 
@@ -65,14 +70,14 @@ def test_soft_forward_backward_hard_leaves(kind, n, A, L, ck, T):
   assert _relerr(eng.dcost[0].cpu().numpy(), dC64) <= RTOL
 
 
-def test_soft_leaves_and_autograd_scaling():
+@pytest.mark.parametrize("ck,n,A,L,T", [("int", 10, 4, 45, 0.8), ("unit", 13, 20, 77, 0.8), ("unit2.5", 8, 3, 66, 1.5)])
+def test_soft_leaves_and_autograd_scaling(ck, n, A, L, T):
   import torch
   from trex_b200.relaxed import soft_sankoff_cost, to_native_leaf_cost
   from trex_b200.sankoff import SankoffEngine
 
   rng = np.random.default_rng(9)
-  n, A, L, T = 10, 4, 45, 0.8
-  adj, cost, _ = _soft_case("random", n, A, L, seed=5, cost_kind="int")
+  adj, cost, _ = _soft_case("random", n, A, L, seed=5, cost_kind=ck)
   n_all = 2 * n - 1
   lc = rng.random((n, L, A)) * 3
   dp64, tot64 = so.soft_sankoff_fwd(adj, cost, lc, n_all, n, T)

@@ -15,22 +15,10 @@
 //  * packed key (integer-valued 0 <= C, max(C)*n_all < 2^18): key = 32*(C[s,t]+d[t]) + t - 15.5
 //    is exact in f32, so one fmin chain (FMNMX3 on sm_100a) yields min AND first argmin.
 #include "common.cuh"
+#include "fwd_params.cuh"
 
 namespace trex {
 
-struct HardFwdParams {
-  const int32_t* plan;
-  size_t plan_words;
-  int n_all, n_leaves, n_states;
-  long long n_sites, stride;
-  const uint8_t* leaf;
-  const float* cost;
-  float* dp;
-  uint8_t* arg;
-  float* root_min;
-  double* total;
-  int mode;
-};
 
 template <int AP>
 struct HardSmem {
@@ -166,6 +154,10 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
   const int tree = blockIdx.y;
   const int n_int = p.n_all - p.n_leaves;
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+  {
+    float a_uni;
+    if (hard_uniform_applies(p, a_uni)) return;  // hard_fwd_uniform_kernel (sankoff_uniform.cu) owns this call
+  }
 
   // ---- prologue: cost matrix, leaf lookup table, fast-path eligibility --------------------
   bool c_ok = true;
@@ -174,7 +166,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
     float c = 0.f;
     if (s < A && t < A) {
       c = __ldg(p.cost + s * A + t);
-      c_ok = c_ok && (c >= 0.f) && (c == truncf(c)) && (c * (float)p.n_all < 262000.f);
+      c_ok = c_ok && fast_cost_ok(c, p.n_all);
     }
     sm.C[i] = c;
   }
@@ -289,6 +281,12 @@ extern "C" int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leave
                   (long long)n_sites, (long long)site_stride, leaf_states, cost, dp, argmin,
                   root_min, total, mode};
   const int A = n_states;
+  {
+    // device-side dispatch on the cost matrix: the O(A) kernel returns at once unless C is uniform
+    // (and mode == AUTO); the general kernels below return at once when it is
+    int rc = launch_hard_fwd_uniform(p, batch, s);
+    if (rc) return rc;
+  }
   if (A <= 2) return launch_hard<2, 4>(p, batch, s);
   if (A <= 4) return launch_hard<4, 4>(p, batch, s);
   if (A <= 8) return launch_hard<8, 2>(p, batch, s);

@@ -10,21 +10,10 @@
 // sum_t K[s,t] e[t] >= exp(-max(C)/T), it cannot underflow while max|C|/T <= 80; otherwise a
 // direct (A*A exp2) evaluation is used.  Leaf rows given as uint8 states are a lookup table.
 #include "common.cuh"
+#include "fwd_params.cuh"
 
 namespace trex {
 
-struct SoftFwdParams {
-  const int32_t* plan;
-  size_t plan_words;
-  int n_all, n_leaves, n_states;
-  long long n_sites, stride;
-  const uint8_t* leaf;
-  const float* leaf_cost;
-  const float* cost;
-  float T;
-  float* dp;
-  double* total;
-};
 
 template <int AP>
 struct SoftFwdSmem {
@@ -141,6 +130,10 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
   const float c1 = 1.4426950408889634f / p.T;   // log2(e)/T
   const float tln2 = p.T * 0.6931471805599453f;  // T*ln(2)
+  {
+    float a_uni;
+    if (soft_uniform_applies(p, a_uni)) return;  // soft_fwd_uniform_kernel (sankoff_uniform.cu) owns this call
+  }
 
   bool c_ok = true;
   for (int i = tid; i < AP * AP; i += THREADS) {
@@ -271,6 +264,10 @@ extern "C" int trex_sankoff_soft_fwd(const int32_t* plan, int n_all, int n_leave
                   (long long)n_sites, (long long)site_stride, leaf_states, leaf_cost, cost,
                   temperature, dp, total};
   const int A = n_states;
+  {
+    int rc = launch_soft_fwd_uniform(p, batch, s);  // returns at once on the device unless C is uniform
+    if (rc) return rc;
+  }
   if (A <= 2) return launch_soft_fwd<2, 4>(p, batch, s);
   if (A <= 4) return launch_soft_fwd<4, 4>(p, batch, s);
   if (A <= 8) return launch_soft_fwd<8, 2>(p, batch, s);
