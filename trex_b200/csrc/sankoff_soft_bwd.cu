@@ -404,9 +404,12 @@ extern "C" int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leave
                   temperature, dp, gscale, gbar, dleaf, dcost, 0};
   const int A = n_states;
   if (A <= 20) {
-    // Device-side dispatch (the cost matrix is device data): the warp-autonomous exp-domain kernel
-    // returns at once when max|C|/T > 80, the direct-evaluation kernel returns at once otherwise.
-    int rc = launch_soft_bwd_warp(p, batch, s);
+    // Device-side dispatch (the cost matrix is device data): the O(A) kernel returns at once unless
+    // the cost is uniform, the warp-autonomous exp-domain kernel returns at once when it is or when
+    // max|C|/T > 80, the direct-evaluation kernel returns at once unless max|C|/T > 80.
+    int rc = launch_soft_bwd_uniform(p, batch, s);
+    if (rc) return rc;
+    rc = launch_soft_bwd_warp(p, batch, s);
     if (rc) return rc;
     p.only_direct = 1;
   }

@@ -86,6 +86,10 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
   const float c1 = 1.4426950408889634f / p.T;
 
+  {
+    float a_uni;
+    if (soft_bwd_uniform_applies(p, a_uni)) return;  // soft_bwd_uniform_kernel owns this call
+  }
   // ---- prologue (whole CTA): K = exp(-C/T), its transpose and row sums ----------------------
   bool c_ok = true;
   for (int i = tid; i < AP * AP; i += 32 * W) {

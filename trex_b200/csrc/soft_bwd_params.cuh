@@ -1,6 +1,7 @@
 // Launch parameters shared by the two relaxed-Sankoff reverse kernels.
 #pragma once
 #include "common.cuh"
+#include "fwd_params.cuh"
 
 namespace trex {
 
@@ -23,6 +24,16 @@ struct SoftBwdParams {
 
 // exp-domain evaluation is valid while exp(-C/T) cannot underflow a whole row sum
 __device__ __forceinline__ bool expdom_ok(float c, float T) { return fabsf(c) <= 80.f * T; }
+
+// true (CTA-wide) when the O(A) kernel of sankoff_soft_bwd_uniform.cu owns this call: uniform cost
+// (fwd_params.cuh), exp-domain evaluation valid, alphabet within the warp kernels' range
+__device__ __forceinline__ bool soft_bwd_uniform_applies(const SoftBwdParams& p, float& a) {
+  const bool uni = cost_is_uniform(p.cost, p.n_states, a);
+  return uni && p.n_states <= 20 && a <= 80.f * p.T;
+}
+
+// sankoff_soft_bwd_uniform.cu: O(A) per edge for a uniform cost (returns at once otherwise)
+int launch_soft_bwd_uniform(const SoftBwdParams& p, int batch, cudaStream_t s);
 
 // sankoff_soft_bwd_warp.cu: warp-autonomous exp-domain kernel (returns at once when !expdom)
 int launch_soft_bwd_warp(const SoftBwdParams& p, int batch, cudaStream_t s);
