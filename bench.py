@@ -166,7 +166,7 @@ def run_reference(args):
     "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     "gpu_launches": 0,
   }
-  print(json.dumps(line), flush=True)
+  emit(line)
 
 
 def workload_config(args, sites_per_rank):
@@ -276,7 +276,7 @@ def run_gpu(args):
   torch.cuda.set_device(local)
   if world > 1:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-  _lib.load()
+  lib = _lib.load()
 
   n, A = N_LEAVES, N_STATES
   n_all = 2 * n - 1
@@ -293,7 +293,6 @@ def run_gpu(args):
   reducer = PackedAllReduce([(1,), (1,), (1, A, A), (1, A, A)], device="cuda")
   packed_h = torch.empty(2 + 2 * A * A, dtype=torch.float64).pin_memory()
   names = ["plan", "hard_fwd", "hard_bwd", "soft_fwd", "soft_bwd", "reduce"]
-  LAUNCHES_PER_STEP = 6  # plan (2 kernels), hard fwd, traceback, soft fwd, soft bwd
 
   def step(ev=None):
     def mark(i):
@@ -331,11 +330,15 @@ def run_gpu(args):
   if rank == 0:
     sampler.start()
   barrier()
+  launches0 = int(lib.trex_kernel_launches())
   e0.record()
   for k in range(args.steps):
     step(evs[k])
   e1.record()
   barrier()
+  # kernels of libtrex_b200.so launched in the timed region, counted by the library itself (the
+  # device-side dispatch launches every candidate kernel of an operator; all but one return at once)
+  gpu_launches = int(lib.trex_kernel_launches()) - launches0
   ms_total = e0.elapsed_time(e1)
   clocks = sampler.stop() if rank == 0 else None
   kern_ms = {nm: float(np.mean([evs[k][i].elapsed_time(evs[k][i + 1]) for k in range(args.steps)]))
@@ -383,8 +386,8 @@ def run_gpu(args):
       roof_all[nm] = {"ms": kern_ms[nm], "alg_bytes": per_site[nm] * L, "achieved": gbs, "frac": gbs / peak}
     dom = max(["hard_fwd", "soft_fwd", "soft_bwd"], key=lambda k: kern_ms[k])
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
-    # (profiles/r01_*_ncu_full.txt), valid for the c5 shape at 100k sites per rank only
-    ncu_traffic = {"hard_fwd": 12.90e9, "soft_fwd": 8.76e9, "soft_bwd": 25.36e9}
+    # (profiles/r01_f_*_ncu_full.txt), valid for the c5 shape at 100k sites per rank only
+    ncu_traffic = {"hard_fwd": 12.79e9, "soft_fwd": 8.71e9, "soft_bwd": 25.26e9}
     traffic = ncu_traffic.get(dom) if (L == N_SITES) else None
     line = {
       "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -399,16 +402,38 @@ def run_gpu(args):
       "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
               "h2d_bytes_per_step": int(states_p.numel() + adj_p.numel() * 4 + cost_p.numel() * 4),
               "d2h_bytes_per_step": int(packed_h.numel() * 8)},
-      "gpu_launches": LAUNCHES_PER_STEP * args.steps,
+      "gpu_launches": gpu_launches,
       "clocks": clocks,
       "results": {"hard_total": float(packed_h[0]), "soft_total": float(packed_h[1])},
     }
     if world == 1 and not args.no_extras:
       line["tree_cost"] = tree_cost_bench(torch)
       line["cpu_baseline"] = cpu_baseline(args.cpu_sites)
-    print(json.dumps(line), flush=True)
+    emit(line)
   if world > 1:
     dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+  """The contract is ONE JSON line on stdout.  Libraries (NCCL's version banner under NCCL_DEBUG, torch
+  warnings) also write to fd 1, so fd 1 is pointed at stderr for the run and the JSON line goes to the
+  saved descriptor."""
+  global _REAL_STDOUT
+  sys.stdout.flush()
+  _REAL_STDOUT = os.dup(1)
+  os.dup2(2, 1)
+
+
+def emit(line):
+  data = (json.dumps(line) + "\n").encode()
+  if _REAL_STDOUT is None:
+    sys.stdout.write(data.decode())
+    sys.stdout.flush()
+  else:
+    os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -423,6 +448,7 @@ def main():
   ap.add_argument("--ref-sites", type=int, default=2048, help="sites per step of --impl reference")
   ap.add_argument("--no-extras", action="store_true", help="skip tree_cost and cpu_baseline legs")
   args = ap.parse_args()
+  quiet_stdout()
   args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
   if args.impl == "reference":
     run_reference(args)

@@ -51,6 +51,9 @@ extern "C" {
 
 TREX_API const char* trex_last_error(void);
 TREX_API int trex_version(void);
+/* Diagnostics: number of CUDA kernels this library has launched in this process (every entry point
+ * counts its own launches).  bench.py reports the difference over its timed region as gpu_launches. */
+TREX_API unsigned long long trex_kernel_launches(void);
 
 /* ---- tree schedule ------------------------------------------------------------------------
  * Replaces the per-node `jnp.where(adj[:, node] == 1, size=2, fill_value=-1)` of

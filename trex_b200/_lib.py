@@ -23,6 +23,7 @@ _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 SIGNATURES = {
   "trex_last_error": (C.c_char_p, []),
   "trex_version": (_i, []),
+  "trex_kernel_launches": (C.c_ulonglong, []),
   "trex_sankoff_plan_words": (C.c_size_t, [_i, _i]),
   "trex_sankoff_plan": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
   "trex_encode_leaf_states": (_i, [_vp, _i, _i64, _i64, _i, _vp, _i64, _vp]),

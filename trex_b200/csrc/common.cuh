@@ -25,6 +25,7 @@ struct PlanView {
 void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 int sm_count();
+void note_launches(int n);  // process-wide count of kernel launches (trex_kernel_launches)
 
 #define TREX_CHECK_ARG(cond, ...)        \
   do {                                   \

@@ -7,6 +7,7 @@
 #include <cstdio>
 
 #include "common.cuh"
+#include <atomic>
 
 namespace trex {
 
@@ -24,6 +25,10 @@ int check_cuda(cudaError_t e, const char* what) {
   set_error("%s: %s", what, cudaGetErrorString(e));
   return TREX_ERR_CUDA;
 }
+
+static std::atomic<unsigned long long> g_kernel_launches{0};
+void note_launches(int n) { g_kernel_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+unsigned long long kernel_launches() { return g_kernel_launches.load(std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached[64] = {0};
@@ -173,6 +178,7 @@ extern "C" {
 
 const char* trex_last_error(void) { return trex::g_err; }
 int trex_version(void) { return 100; }
+unsigned long long trex_kernel_launches(void) { return trex::kernel_launches(); }
 
 size_t trex_sankoff_plan_words(int n_all, int n_leaves) {
   const int n_int = n_all - n_leaves;
@@ -192,8 +198,10 @@ int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
   dim3 grid((n_int + kColsPerCta - 1) / kColsPerCta, batch);
   dim3 block(kColsPerCta, kRowChunks);
   plan_children_kernel<<<grid, block, 0, s>>>(adj, n_all, n_leaves, zero_root_selfloop, plan, words);
+  note_launches(1);
   TREX_CHECK_LAUNCH("plan_children_kernel");
   plan_order_kernel<<<batch, 32, 0, s>>>(n_all, n_leaves, plan, words);
+  note_launches(1);
   TREX_CHECK_LAUNCH("plan_order_kernel");
   return TREX_OK;
 }

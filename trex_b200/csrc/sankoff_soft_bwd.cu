@@ -369,9 +369,11 @@ static int launch_soft_bwd(const SoftBwdParams& p, int batch, cudaStream_t s) {
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd)");
     kern<<<grid, THREADS, smem, s>>>(p);
+    note_launches(1);
   } else {
     auto kern = soft_bwd_kernel<AP, V, THREADS, false>;
     kern<<<grid, THREADS, smem, s>>>(p);
+    note_launches(1);
   }
   return check_cuda(cudaPeekAtLastError(), "soft_bwd_kernel");
 }

@@ -493,7 +493,7 @@ int launch_uniform(const SoftBwdParams& p, int batch, cudaStream_t s) {
   dim3 grid((unsigned)((p.n_sites + Cfg::NS - 1) / Cfg::NS), batch);
   auto go = [&](auto kern) -> cudaError_t {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess) kern<<<grid, 32, smem, s>>>(p);
+    if (e == cudaSuccess) { kern<<<grid, 32, smem, s>>>(p); note_launches(1); }
     return e;
   };
   const bool full = p.n_states == AP;

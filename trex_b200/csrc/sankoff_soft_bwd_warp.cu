@@ -490,11 +490,13 @@ static int launch_warp(const SoftBwdParams& p, int batch, cudaStream_t s) {
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd_warp)");
     kern<<<grid, 32 * W, smem, s>>>(p);
+    note_launches(1);
   } else {
     auto kern = soft_bwd_warp_kernel<AP, V, W, false>;
     e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd_warp)");
     kern<<<grid, 32 * W, smem, s>>>(p);
+    note_launches(1);
   }
   return check_cuda(cudaPeekAtLastError(), "soft_bwd_warp_kernel");
 }

@@ -235,6 +235,7 @@ static int launch_soft_fwd(const SoftFwdParams& p, int batch, cudaStream_t s) {
   const long long nvec = (p.n_sites + V - 1) / V;
   dim3 grid((unsigned)((nvec + THREADS - 1) / THREADS), batch);
   soft_fwd_kernel<AP, V, THREADS><<<grid, THREADS, 0, s>>>(p);
+  note_launches(1);
   return check_cuda(cudaPeekAtLastError(), "soft_fwd_kernel");
 }
 

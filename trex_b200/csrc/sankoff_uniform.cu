@@ -392,11 +392,11 @@ void launch_hard_uniform(const HardFwdParams& p, int batch, cudaStream_t s) {
   const dim3 grid((unsigned)((p.n_sites + (long long)T * V - 1) / ((long long)T * V)), batch);
   const bool full = p.n_states == AP;
   if (p.arg) {
-    if (full) hard_fwd_uniform_kernel<AP, V, T, true, true><<<grid, T, 0, s>>>(p);
-    else hard_fwd_uniform_kernel<AP, V, T, false, true><<<grid, T, 0, s>>>(p);
+    if (full) { hard_fwd_uniform_kernel<AP, V, T, true, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+    else { hard_fwd_uniform_kernel<AP, V, T, false, true><<<grid, T, 0, s>>>(p); note_launches(1); }
   } else {
-    if (full) hard_fwd_uniform_kernel<AP, V, T, true, false><<<grid, T, 0, s>>>(p);
-    else hard_fwd_uniform_kernel<AP, V, T, false, false><<<grid, T, 0, s>>>(p);
+    if (full) { hard_fwd_uniform_kernel<AP, V, T, true, false><<<grid, T, 0, s>>>(p); note_launches(1); }
+    else { hard_fwd_uniform_kernel<AP, V, T, false, false><<<grid, T, 0, s>>>(p); note_launches(1); }
   }
 }
 }  // namespace
@@ -415,8 +415,8 @@ template <int AP, int V>
 void launch_soft_uniform(const SoftFwdParams& p, int batch, cudaStream_t s) {
   constexpr int T = 128;
   const dim3 grid((unsigned)((p.n_sites + (long long)T * V - 1) / ((long long)T * V)), batch);
-  if (p.n_states == AP) soft_fwd_uniform_kernel<AP, V, T, true><<<grid, T, 0, s>>>(p);
-  else soft_fwd_uniform_kernel<AP, V, T, false><<<grid, T, 0, s>>>(p);
+  if (p.n_states == AP) { soft_fwd_uniform_kernel<AP, V, T, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+  else { soft_fwd_uniform_kernel<AP, V, T, false><<<grid, T, 0, s>>>(p); note_launches(1); }
 }
 }  // namespace
 

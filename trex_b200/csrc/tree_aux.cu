@@ -173,6 +173,7 @@ int trex_update_seq_fwd(const float* logits, int n_ancestors, int64_t n_sites, i
   if (rows == 0) return TREX_OK;
   update_seq_fwd_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       logits, rows, n_states, temperature, seqs_ancestor_rows);
+  note_launches(1);
   TREX_CHECK_LAUNCH("update_seq_fwd_kernel");
   return TREX_OK;
 }
@@ -187,6 +188,7 @@ int trex_update_seq_bwd(const float* seqs_ancestor_rows, const float* d_seqs_anc
   if (rows == 0) return TREX_OK;
   update_seq_bwd_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       seqs_ancestor_rows, d_seqs_ancestor_rows, rows, n_states, temperature, d_logits);
+  note_launches(1);
   TREX_CHECK_LAUNCH("update_seq_bwd_kernel");
   return TREX_OK;
 }
@@ -198,6 +200,7 @@ int trex_update_tree_fwd(const float* tree_params, const float* gumbel_noise, co
                  "trex_update_tree_fwd: bad arguments (n_ancestors == 0 is handled by the caller: eye)");
   update_tree_fwd_kernel<<<n_nodes, 128, 0, (cudaStream_t)stream>>>(tree_params, gumbel_noise, gates, temperature,
                                                                     n_nodes, n_leaves, adjacency);
+  note_launches(1);
   TREX_CHECK_LAUNCH("update_tree_fwd_kernel");
   return TREX_OK;
 }
@@ -209,6 +212,7 @@ int trex_update_tree_bwd(const float* adjacency, const float* d_adjacency, const
                  "trex_update_tree_bwd: bad arguments");
   update_tree_bwd_kernel<<<n_nodes - 1, 128, 0, (cudaStream_t)stream>>>(adjacency, d_adjacency, gates, temperature,
                                                                         n_nodes, n_leaves, d_tree_params);
+  note_launches(1);
   TREX_CHECK_LAUNCH("update_tree_bwd_kernel");
   return TREX_OK;
 }
@@ -227,8 +231,10 @@ int trex_graph_constraint(const float* adjacency, int n_nodes, float scaling_fac
     if (rc) return rc;
   }
   graph_constraint_kernel<<<n_anc, 128, 0, s>>>(adjacency, n_nodes, n_anc, scaling_factor, scratch, d_adjacency);
+  note_launches(1);
   TREX_CHECK_LAUNCH("graph_constraint_kernel");
   finish_scalar_kernel<<<1, 1, 0, s>>>(scratch, out_loss);
+  note_launches(1);
   TREX_CHECK_LAUNCH("finish_scalar_kernel");
   return TREX_OK;
 }
@@ -239,8 +245,10 @@ int trex_discretize_topology(const float* adjacency, int n_nodes, int32_t* paren
   TREX_CHECK_ARG(adjacency && parent_scratch && one_hot && n_nodes >= 1, "trex_discretize_topology: bad arguments");
   cudaStream_t s = (cudaStream_t)stream;
   row_argmax_kernel<<<(n_nodes + 127) / 128, 128, 0, s>>>(adjacency, n_nodes, n_nodes, parent_scratch);
+  note_launches(1);
   TREX_CHECK_LAUNCH("row_argmax_kernel");
   one_hot_rows_kernel<<<n_nodes, 128, 0, s>>>(parent_scratch, n_nodes, one_hot);
+  note_launches(1);
   TREX_CHECK_LAUNCH("one_hot_rows_kernel");
   return TREX_OK;
 }
@@ -257,15 +265,19 @@ int trex_compute_cost(const float* seqs_one_hot, const float* adjacency, const f
   int rc = check_cuda(cudaMemsetAsync(acc_scratch, 0, sizeof(double), s), "memset");
   if (rc) return rc;
   row_argmax_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(seqs_one_hot, rows, n_states, state_scratch);
+  note_launches(1);
   TREX_CHECK_LAUNCH("row_argmax_kernel");
   row_argmax_kernel<<<(n_nodes + 127) / 128, 128, 0, s>>>(adjacency, n_nodes, n_nodes, parent_scratch);
+  note_launches(1);
   TREX_CHECK_LAUNCH("row_argmax_kernel");
   if (n_nodes > 1) {
     dim3 grid((unsigned)((n_sites + 255) / 256), n_nodes - 1);  // [:-1] drops the last node
     compute_cost_kernel<<<grid, 256, 0, s>>>(state_scratch, parent_scratch, subst, n_nodes, n_sites, n_states, acc_scratch);
+    note_launches(1);
     TREX_CHECK_LAUNCH("compute_cost_kernel");
   }
   finish_scalar_kernel<<<1, 1, 0, s>>>(acc_scratch, out_cost);
+  note_launches(1);
   TREX_CHECK_LAUNCH("finish_scalar_kernel");
   return TREX_OK;
 }

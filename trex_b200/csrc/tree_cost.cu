@@ -291,6 +291,7 @@ int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cos
   if (tc::supported(N, cost_kind)) return tc::run(seqs, adj, N, K, out_cost, d_seqs, d_adj, workspace, s);
   TcWorkspace w = tc_carve(workspace, N, Q);
   tc_prologue_kernel<<<N, 128, 0, s>>>(adj, N, Q, w);
+  note_launches(1);
   TREX_CHECK_LAUNCH("tc_prologue_kernel");
   const int spc = kKcMax / Q > 0 ? kKcMax / Q : 1;  // whole sites per staged chunk
   const int kc = spc * Q;
@@ -304,6 +305,7 @@ int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cos
     parts = (nchunks + chunks_per_part - 1) / chunks_per_part;
     dim3 grid((unsigned)parts, tiles, tiles);
     tc_gram_kernel<<<grid, 256, 0, s>>>(seqs, cost, cost_kind, N, K, Q, kc, chunks_per_part * kc, w);
+    note_launches(1);
     TREX_CHECK_LAUNCH("tc_gram_kernel");
   }
   const bool want_dc = d_cost != nullptr && cost_kind != 0;
@@ -316,12 +318,14 @@ int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cos
                         "cudaFuncSetAttribute(tc_ds_kernel)");
     if (rc) return rc;
     tc_ds_kernel<<<grid, 256, smem, s>>>(seqs, adj, cost, cost_kind, N, K, Q, kc, d_seqs, want_dc, w);
+    note_launches(1);
     TREX_CHECK_LAUNCH("tc_ds_kernel");
   }
   {
     const long long n2 = (long long)N * N;
     tc_finalize_kernel<<<(unsigned)((n2 + 255) / 256), 256, 0, s>>>(adj, N, Q, cost_kind, out_cost, d_adj,
                                                                     d_cost, w);
+    note_launches(1);
     TREX_CHECK_LAUNCH("tc_finalize_kernel");
   }
   return TREX_OK;

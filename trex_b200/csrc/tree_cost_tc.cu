@@ -482,6 +482,7 @@ static int launch_gemm(const TcBuffers& w, const GemmParams& gp, cudaStream_t st
                   "cudaFuncSetAttribute(tc_gemm_kernel)");
   if (rc) return rc;
   kern<<<gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds, 128, GemmCfg<NPAD>::SMEM_BYTES, stream>>>(ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo, gp);
+  note_launches(1);
   return check_cuda(cudaPeekAtLastError(), "tc_gemm_kernel");
 }
 
@@ -491,6 +492,7 @@ int run(const float* seqs, const float* adj, int n_nodes, long long k, float* ou
   const long long tiles = (long long)(w.npad / 32) * (w.kp / 32);
   TREX_CHECK_ARG(w.npad + tiles <= 2147483647LL, "tree_cost(tcgen05): K too large");
   prep_kernel<<<(unsigned)(w.npad + tiles), 256, 0, stream>>>(seqs, adj, n_nodes, k, w);
+  note_launches(1);
   TREX_CHECK_LAUNCH("tc::prep_kernel");
   GemmParams gp{};
   gp.n_nodes = n_nodes;
@@ -502,6 +504,7 @@ int run(const float* seqs, const float* adj, int n_nodes, long long k, float* ou
   int rc = w.npad == 128 ? launch_gemm<128>(w, gp, stream) : launch_gemm<256>(w, gp, stream);
   if (rc) return rc;
   final_kernel<<<n_nodes, 256, 0, stream>>>(adj, n_nodes, w, out_cost, d_adj);
+  note_launches(1);
   TREX_CHECK_LAUNCH("tc::final_kernel");
   return TREX_OK;
 }
