@@ -196,3 +196,42 @@ def test_tree_cost_tcgen05_and_simt_paths_agree_with_oracle(N, L, Q, monkeypatch
   monkeypatch.setenv("TREX_TREE_COST_PATH", "auto")
   cost, dS, dA, _ = tree_cost_value_and_grad(St, At, None, want_dseq=False, want_dadj=False)
   assert dS is None and dA is None and abs(float(cost) - want) <= bound
+
+
+@pytest.mark.parametrize("n,A,L", [(256, 20, 10_000), (128, 4, 5_000)])
+def test_full_size_relaxed_properties(n, A, L):
+  """Sizes of BASELINE configs c3 / c4 (one tree): size-independent properties of the relaxed path.
+  * every node's cotangent row sums to 1 (softmin weights are a distribution, so mass is conserved
+    from the root down) and every leaf receives mass 1 per site;
+  * sum(dC) = number of edges x sites;
+  * the O(A) uniform-cost kernels (C = 1 - I) and the general exp-domain kernels (same C with one entry
+    moved by 1e-6, which changes the device-side dispatch and nothing else) agree to 1e-5."""
+  import torch
+  from trex_b200.sankoff import SankoffEngine
+
+  rng = np.random.default_rng(n * 3 + A)
+  par = synth.balanced_parents(n)
+  adj = synth.parents_to_adjacency(par)
+  states = synth.evolve(par, L, A, 0.1, rng)[:n]
+  n_all, T = 2 * n - 1, 1.0
+  cost = synth.unit_cost(A)
+  cost_g = cost.copy()
+  cost_g[0, 1] += 1e-6
+  out = []
+  for c in (cost, cost_g):
+    eng = SankoffEngine(n_all, n, A, L)
+    eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states))
+    tot = float(eng.soft_forward(torch.from_numpy(c), T)[0])
+    eng.soft_backward(torch.from_numpy(c), T)
+    out.append((tot, eng.soft_dp[..., :L].clone(), eng.gbar[..., :L].clone(), eng.dleaf[..., :L].clone(),
+                eng.dcost[0].clone()))
+    del eng
+  (t0, dp0, g0, dl0, dc0), (t1, dp1, g1, dl1, dc1) = out
+  assert torch.allclose(g0.sum(dim=2), torch.ones_like(g0[:, :, 0]), atol=2e-5)
+  assert torch.allclose(dl0.sum(dim=2), torch.ones_like(dl0[:, :, 0]), atol=2e-5)
+  assert abs(float(dc0.sum()) - 2 * (n - 1) * L) <= 1e-5 * 2 * (n - 1) * L
+  assert abs(t0 - t1) <= RTOL * abs(t0)
+  assert float((dp0 - dp1).abs().max()) <= RTOL * float(dp0.abs().max())
+  assert float((g0 - g1).abs().max()) <= 2 * RTOL
+  assert float((dl0 - dl1).abs().max()) <= 2 * RTOL
+  assert float((dc0 - dc1).abs().max()) <= RTOL * float(dc0.abs().max())
