@@ -107,6 +107,12 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// Programmatic dependent launch: the three kernels of a call are chained in one stream; a dependent grid
+// may start (prologue: barrier init, TMEM allocation, tensor-map prefetch) while its predecessor drains,
+// and blocks in pdl_wait() until the predecessor has completed and its writes are visible.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // K-major operand tile in shared memory, rows of 128 bytes (32 tf32), 128B swizzle as written by
 // TMA: 8-row groups are 1024 bytes apart (SBO); descriptor version 1 (Blackwell).
 __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
@@ -161,6 +167,7 @@ __global__ void __launch_bounds__(256)
       w.g[(size_t)i * npad + j] = 0.f;
     }
     if (i == 0 && tid == 0) { *w.cost = 0.0; *w.ticket = 0u; }
+    pdl_launch_dependents();  // at the END: a waiting GEMM CTA holds ~200 KB of shared memory on its SM
     return;
   }
   // ---- S -> S_hi/S_lo [npad][Kp] and ST_hi/ST_lo [Kp][npad]: 32 x 32 tiles through smem ----------
@@ -188,6 +195,7 @@ __global__ void __launch_bounds__(256)
     w.st_hi[(size_t)col * npad + row] = t_hi[tx][r];
     w.st_lo[(size_t)col * npad + row] = t_lo[tx][r];
   }
+  pdl_launch_dependents();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -248,6 +256,8 @@ __global__ void __launch_bounds__(128, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  pdl_launch_dependents();
+  pdl_wait();  // everything below reads what the prep kernel wrote
 
   int it0, it1;  // k-block range (gram) / j-block range (dS)
   if (is_gram) {
@@ -354,12 +364,15 @@ __global__ void __launch_bounds__(256)
   __shared__ float diag[kMaxNodes];
   const int i = blockIdx.x, tid = threadIdx.x;
   const int npad = w.npad;
+  const float a_pre = tid < N ? adj[(size_t)i * N + tid] : 0.f;  // inputs only: may be read before the wait
+  pdl_wait();  // G is complete once the GEMM grid has finished
   for (int j = tid; j < N; j += 256) diag[j] = w.g[(size_t)j * npad + j];
+  const float g_pre = tid < N ? w.g[(size_t)i * npad + tid] : 0.f;
   __syncthreads();
   double part = 0.0;
   for (int j = tid; j < N; j += 256) {
-    const float g = w.g[(size_t)i * npad + j];
-    const float a = adj[(size_t)i * N + j];
+    const float g = j == tid ? g_pre : w.g[(size_t)i * npad + j];
+    const float a = j == tid ? a_pre : adj[(size_t)i * N + j];
     const double m = (i == j ? (double)w.d[i] : 0.0) - (double)a;
     part += m * (double)g;
     if (d_adj) d_adj[(size_t)i * N + j] = 0.5f * (diag[i] + diag[j]) - g;
@@ -467,6 +480,22 @@ static int make_map(CUtensorMap* map, float* base, long long rows, long long col
   return TREX_OK;
 }
 
+// launch configuration with programmatic stream serialization (the kernel may start before its
+// predecessor in the stream has finished; it synchronises with pdl_wait())
+static cudaLaunchAttribute g_pdl_attr;
+static cudaLaunchConfig_t pdl_config(dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
+  g_pdl_attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  g_pdl_attr.val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cfg.attrs = &g_pdl_attr;
+  cfg.numAttrs = 1;
+  return cfg;
+}
+
 template <int NPAD>
 static int launch_gemm(const TcBuffers& w, const GemmParams& gp, cudaStream_t stream) {
   CUtensorMap ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo;
@@ -481,9 +510,10 @@ static int launch_gemm(const TcBuffers& w, const GemmParams& gp, cudaStream_t st
   rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<NPAD>::SMEM_BYTES),
                   "cudaFuncSetAttribute(tc_gemm_kernel)");
   if (rc) return rc;
-  kern<<<gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds, 128, GemmCfg<NPAD>::SMEM_BYTES, stream>>>(ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo, gp);
+  cudaLaunchConfig_t cfg = pdl_config(dim3(gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds), dim3(128), GemmCfg<NPAD>::SMEM_BYTES, stream);
+  rc = check_cuda(cudaLaunchKernelEx(&cfg, kern, ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo, gp), "tc_gemm_kernel");
   note_launches(1);
-  return check_cuda(cudaPeekAtLastError(), "tc_gemm_kernel");
+  return rc;
 }
 
 int run(const float* seqs, const float* adj, int n_nodes, long long k, float* out_cost, float* d_seqs, float* d_adj,
@@ -503,10 +533,10 @@ int run(const float* seqs, const float* adj, int n_nodes, long long k, float* ou
   gp.d_seqs = d_seqs;
   int rc = w.npad == 128 ? launch_gemm<128>(w, gp, stream) : launch_gemm<256>(w, gp, stream);
   if (rc) return rc;
-  final_kernel<<<n_nodes, 256, 0, stream>>>(adj, n_nodes, w, out_cost, d_adj);
+  cudaLaunchConfig_t cfg = pdl_config(dim3(n_nodes), dim3(256), 0, stream);
+  rc = check_cuda(cudaLaunchKernelEx(&cfg, final_kernel, adj, n_nodes, w, out_cost, d_adj), "tc::final_kernel");
   note_launches(1);
-  TREX_CHECK_LAUNCH("tc::final_kernel");
-  return TREX_OK;
+  return rc;
 }
 
 }  // namespace tc
