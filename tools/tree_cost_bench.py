@@ -17,6 +17,9 @@ from trex_b200 import _lib  # noqa: E402
 from trex_b200.tree import tree_cost_value_and_grad  # noqa: E402
 
 
+STEPS_PER_GRAPH = int(os.environ.get("STEPS_PER_GRAPH", "1"))
+
+
 def case(N, L, Q, seed, iters):
   rng = np.random.default_rng(seed)
   S = to.softmax(rng.normal(size=(N, L, Q))).astype(np.float32)
@@ -38,7 +41,8 @@ def case(N, L, Q, seed, iters):
     g = torch.cuda.CUDAGraph()
     stream.synchronize()
     with torch.cuda.graph(g, stream=stream):
-      tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
+      for _ in range(STEPS_PER_GRAPH):
+        tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
     g.replay()
     stream.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -47,7 +51,7 @@ def case(N, L, Q, seed, iters):
       g.replay()
     e1.record(stream)
     stream.synchronize()
-  ms = e0.elapsed_time(e1) / iters
+  ms = e0.elapsed_time(e1) / iters / STEPS_PER_GRAPH
   K = L * Q
   flop = 4.0 * N * N * K
   return {"N": N, "L": L, "Q": Q, "us_per_step": ms * 1e3, "grad_steps_per_s": 1e3 / ms,

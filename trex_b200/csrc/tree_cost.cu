@@ -288,7 +288,7 @@ int trex_tree_cost_fwd_bwd(const float* seqs, const float* adj, const float* cos
   const long long K = (long long)n_sites * Q;
   cudaStream_t s = (cudaStream_t)stream;
   // identity cost, N <= 256: tcgen05 / TMEM / TMA path (3xTF32); everything else: exact-f32 CUDA cores
-  if (tc::supported(N, cost_kind)) return tc::run(seqs, adj, N, K, out_cost, d_seqs, d_adj, workspace, s);
+  if (tc::supported(seqs, N, K, cost_kind)) return tc::run(seqs, adj, N, K, out_cost, d_seqs, d_adj, workspace, s);
   TcWorkspace w = tc_carve(workspace, N, Q);
   tc_prologue_kernel<<<N, 128, 0, s>>>(adj, N, Q, w);
   note_launches(1);

@@ -10,13 +10,16 @@
 // x = hi + lo (hi = x with the low 13 mantissa bits cleared, lo = x - hi, both exact) and each
 // product is evaluated as hi*hi + hi*lo + lo*hi into the same accumulator (3xTF32).
 //
-//   prep kernel : d, M + M^T (hi/lo), S -> S_hi/S_lo [Npad][Kp] and transposed ST_hi/ST_lo [Kp][Npad]
+//   prep kernel : d, M + M^T (hi/lo), zero G
 //   gemm kernel : CTA role by blockIdx —
 //                 gram CTAs: split-K slice of G = S S^T  -> G by 128-bit red.global.add.v4.f32
-//                 dS   CTAs: 128 columns of dS^T = ST (M + M^T)  -> dS (coalesced along K)
-//                 TMA (128B swizzle) -> 2..3-stage mbarrier ring -> single-thread tcgen05.mma ->
-//                 tcgen05.commit -> all four warps read TMEM with tcgen05.ld
-//   final kernel: cost = <M, G>, dAdj.
+//                 dS   CTAs: 128 columns of dS^T = S^T (M + M^T)  -> dS (coalesced along K)
+//                 S is read raw by TMA (128B swizzle; MN-major 32-byte-atom swizzle for the dS role, so
+//                 no transposed copy exists), converter warps write the tf32 remainder tile, the raw
+//                 tile serves as the head (the tensor core reads the top 19 bits) -> 2..3-stage
+//                 mbarrier ring -> single-thread tcgen05.mma -> tcgen05.commit -> tcgen05.ld epilogue
+//   final kernel: cost = <M, G>, dAdj (folded into the last gram CTA for N <= 64).
+// The three launches are chained with programmatic dependent launch.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -113,8 +116,13 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
-// K-major operand tile in shared memory, rows of 128 bytes (32 tf32), 128B swizzle as written by
-// TMA: 8-row groups are 1024 bytes apart (SBO); descriptor version 1 (Blackwell).
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Shared-memory matrix descriptors (version 1 = Blackwell), 128B swizzle as written by TMA.
+// K-major tile: rows of 128 bytes (32 tf32 along K), 8-row groups 1024 bytes apart (SBO); a K step of
+// 8 tf32 advances the start address by 32 bytes.
 __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);  // start address
@@ -124,130 +132,136 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
   return d;
 }
-// kind::tf32, fp32 accumulate, both operands K-major
-__host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n) {
-  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+// MN-major tile (the contraction index runs over ROWS).  For 32-bit operands the only MN-major layout
+// the tensor core accepts is "128B swizzle with a 32-byte atom" (layout type 1; TMA writes it with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): rows of 128 bytes (32 values of M), the 32-byte chunks of a row
+// XOR-ed with (row & 3), so the swizzle repeats every 4 rows = 512 bytes (SBO).  Each TMA box is
+// [32 K-rows][128 bytes of M]; the 128 M values of one MMA span four boxes 4096 bytes apart (LBO).
+// A K step of 8 rows advances the start address by 1024 bytes.
+__device__ __forceinline__ uint64_t make_mnmajor_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
+  d |= (uint64_t)(4096 >> 4) << 16;            // LBO: next 32-wide chunk of M
+  d |= (uint64_t)(512 >> 4) << 32;             // SBO: next 4 rows of K
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)1 << 61;                      // SWIZZLE_128B_BASE32B
+  return d;
+}
+// kind::tf32, fp32 accumulate; B is K-major, A is K-major or MN-major (bit 15)
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n, bool a_mn_major) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
 // ---------------------------------------------------------------------------------------------
-// prep kernel
+// prep kernel: row i of Msym = M + M^T (tf32 head / remainder), d_i, zero G.  grid = Npad, block = 256
 // ---------------------------------------------------------------------------------------------
-// grid.x = Npad (rows of M + M^T, d, zeroing) + transpose tiles; block = 256
 __global__ void __launch_bounds__(256)
-    prep_kernel(const float* __restrict__ S, const float* __restrict__ adj, int N, long long K, TcBuffers w) {
+    prep_kernel(const float* __restrict__ adj, int N, TcBuffers w) {
   const int tid = threadIdx.x;
   const int npad = w.npad;
-  if ((int)blockIdx.x < npad) {
-    // ---- row i of Msym = M + M^T (hi/lo), d_i ------------------------------------------------
-    const int i = blockIdx.x;
-    __shared__ float red[8];
-    __shared__ float s_d;
-    float acc = 0.f;
-    if (i < N)
-      for (int j = tid; j < N; j += 256) acc += adj[(size_t)i * N + j] + adj[(size_t)j * N + i];
+  const int i = blockIdx.x;
+  pdl_launch_dependents();  // the GEMM grid may start now: its gram CTAs need this kernel only at their epilogue
+  __shared__ float red[8];
+  __shared__ float s_d;
+  float acc = 0.f;
+  if (i < N)
+    for (int j = tid; j < N; j += 256) acc += adj[(size_t)i * N + j] + adj[(size_t)j * N + i];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if ((tid & 31) == 0) red[tid >> 5] = acc;
-    __syncthreads();
-    if (tid == 0) {
-      float t = 0.f;
-      for (int q = 0; q < 8; ++q) t += red[q];
-      s_d = 0.5f * t;
-      if (i < N) w.d[i] = s_d;
-    }
-    __syncthreads();
-    for (int j = tid; j < npad; j += 256) {
-      float m = 0.f;
-      if (i < N && j < N) m = (i == j ? 2.f * s_d : 0.f) - adj[(size_t)i * N + j] - adj[(size_t)j * N + i];
-      const float hi = tf32_hi(m);
-      w.m_hi[(size_t)i * npad + j] = hi;
-      w.m_lo[(size_t)i * npad + j] = m - hi;
-      w.g[(size_t)i * npad + j] = 0.f;
-    }
-    if (i == 0 && tid == 0) { *w.cost = 0.0; *w.ticket = 0u; }
-    pdl_launch_dependents();  // at the END: a waiting GEMM CTA holds ~200 KB of shared memory on its SM
-    return;
-  }
-  // ---- S -> S_hi/S_lo [npad][Kp] and ST_hi/ST_lo [Kp][npad]: 32 x 32 tiles through smem ----------
-  __shared__ float t_hi[32][33], t_lo[32][33];
-  const long long tile = (long long)blockIdx.x - npad;
-  const int row_tiles = npad / 32;
-  const long long kt = tile / row_tiles;
-  const int rt = (int)(tile % row_tiles);
-  const int tx = tid & 31, ty = tid >> 5;  // 32 x 8
-  for (int r = ty; r < 32; r += 8) {
-    const int row = rt * 32 + r;
-    const long long col = kt * 32 + tx;
-    float x = 0.f;
-    if (row < N && col < K) x = S[(size_t)row * K + col];
-    const float hi = tf32_hi(x), lo = x - hi;
-    w.s_hi[(size_t)row * w.kp + col] = hi;
-    w.s_lo[(size_t)row * w.kp + col] = lo;
-    t_hi[r][tx] = hi;
-    t_lo[r][tx] = lo;
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((tid & 31) == 0) red[tid >> 5] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    float t = 0.f;
+    for (int q = 0; q < 8; ++q) t += red[q];
+    s_d = 0.5f * t;
+    if (i < N) w.d[i] = s_d;
   }
   __syncthreads();
-  for (int r = ty; r < 32; r += 8) {
-    const long long col = kt * 32 + r;  // row of ST
-    const int row = rt * 32 + tx;       // column of ST
-    w.st_hi[(size_t)col * npad + row] = t_hi[tx][r];
-    w.st_lo[(size_t)col * npad + row] = t_lo[tx][r];
+  for (int j = tid; j < npad; j += 256) {
+    float m = 0.f;
+    if (i < N && j < N) m = (i == j ? 2.f * s_d : 0.f) - adj[(size_t)i * N + j] - adj[(size_t)j * N + i];
+    const float hi = tf32_hi(m);
+    w.m_hi[(size_t)i * npad + j] = hi;
+    w.m_lo[(size_t)i * npad + j] = m - hi;
+    w.g[(size_t)i * npad + j] = 0.f;
   }
-  pdl_launch_dependents();
+  if (i == 0 && tid == 0) { *w.cost = 0.0; *w.ticket = 0u; }
 }
 
 // ---------------------------------------------------------------------------------------------
-// tcgen05 GEMM kernel: gram CTAs (split-K of G = S S^T) and dS CTAs (dS^T = ST (M + M^T))
+// tcgen05 GEMM kernel: gram CTAs (split-K of G = S S^T) and dS CTAs (dS^T = S^T (M + M^T))
 // ---------------------------------------------------------------------------------------------
+// S is read ONCE, raw, straight from the caller's tensor: TMA drops f32 tiles into shared memory,
+// four converter warps split them in place into the tf32 head (hi) and the exact remainder (lo) — the
+// split is elementwise, so it commutes with the 128B swizzle — and hand the stage to the MMA thread
+// through a second mbarrier (generic-proxy writes are fenced for the async proxy first).
+//  * gram unit: tile = [Npad node rows][32 columns of K], K-major; A is the 128-row block of the
+//    same tile, so G = S S^T needs no second operand.
+//  * dS unit (128 columns of S): A = S itself as an MN-major operand (rows = nodes = contraction
+//    index), four [32 rows][32 columns] boxes per step; B = Msym rows (K-major).  D = dS^T tile, stored
+//    with lanes along K, i.e. coalesced rows of dS.  No transposed copy of S exists anywhere.
 template <int NPAD>
 struct GemmCfg {
   static constexpr int MBLK = NPAD / 128;                         // M blocks of the gram accumulator
-  static constexpr int BK = 32;                                   // tf32 per k-block = one 128 B swizzle row
-  static constexpr int A_BYTES = 128 * 128;                       // 128 rows x 128 B (dS role only)
-  static constexpr int B_BYTES = NPAD * 128;
+  static constexpr int BK = 32;                                   // contraction elements per pipeline step
+  static constexpr int A_BYTES = 128 * 128;                       // dS role: 4 boxes of [32 rows][128 B]
+  static constexpr int B_BYTES = NPAD * 128;                      // [Npad rows][128 B]
   static constexpr int STAGE_BYTES = 2 * A_BYTES + 2 * B_BYTES;   // A_hi, A_lo, B_hi, B_lo
   static constexpr int STAGES = NPAD == 128 ? 3 : 2;
   static constexpr int TMEM_COLS = NPAD;                          // one 128 x NPAD fp32 accumulator
+  static constexpr int THREADS = 256;                             // warp 0: TMA, warp 1: MMA, warps 2-7: converters, 0-3: epilogue
+  static constexpr int CONV_WARPS = 6;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
 struct GemmParams {
   int n_nodes;
-  long long k;          // true contraction length (columns of S)
-  int n_gram;           // gram CTAs = slabs
-  int kb_per_gram;      // k-blocks per gram CTA
+  long long k;          // contraction length of the Gram product (columns of S)
+  int n_gram;           // gram units = split-K slices
+  int kb_per_gram;      // k-blocks per gram unit
   int n_kb;             // ceil(k / 32)
-  int n_ds;             // dS CTAs = ceil(k / 128), 0 when d_seqs is not wanted
+  int n_ds;             // dS units = ceil(k / 128), 0 when d_seqs is not wanted
   float* g;             // [NPAD][NPAD] G = S S^T, zeroed by the prep kernel
   float* d_seqs;        // [N][K]
+  // fused finalisation (small N): the gram CTA that finishes last forms <M, G> and dAdj itself
+  int fuse_final;
+  const float* adj;
+  const float* d;       // [N] from the prep kernel
+  unsigned* ticket;     // zeroed by the prep kernel
+  float* out_cost;
+  float* d_adj;
 };
 
 template <int NPAD>
-__global__ void __launch_bounds__(128, 1)
-    tc_gemm_kernel(const __grid_constant__ CUtensorMap map_s_hi, const __grid_constant__ CUtensorMap map_s_lo,
-                   const __grid_constant__ CUtensorMap map_st_hi, const __grid_constant__ CUtensorMap map_st_lo,
+__global__ void __launch_bounds__(256, 1)
+    tc_gemm_kernel(const __grid_constant__ CUtensorMap map_s_gram, const __grid_constant__ CUtensorMap map_s_ds,
                    const __grid_constant__ CUtensorMap map_m_hi, const __grid_constant__ CUtensorMap map_m_lo,
                    const GemmParams p) {
   using Cfg = GemmCfg<NPAD>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* tiles = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tiles + Cfg::STAGES * Cfg::STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + Cfg::STAGES;
+  uint64_t* conv_bar = full_bar + Cfg::STAGES;
+  uint64_t* empty_bar = conv_bar + Cfg::STAGES;
   uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const bool is_gram = (int)blockIdx.x < p.n_gram * Cfg::MBLK;   // gram unit = (slab, M block)
+  const bool is_gram = (int)blockIdx.x < p.n_gram * Cfg::MBLK;   // gram unit = (slice, M block)
   const int unit = is_gram ? blockIdx.x / Cfg::MBLK : blockIdx.x - p.n_gram * Cfg::MBLK;
   const int mblk = is_gram ? blockIdx.x % Cfg::MBLK : 0;
 
   if (warp == 0 && lane == 0) {
-    prefetch_tmap(is_gram ? &map_s_hi : &map_st_hi);
-    prefetch_tmap(is_gram ? &map_s_lo : &map_st_lo);
+    prefetch_tmap(is_gram ? &map_s_gram : &map_s_ds);
     if (!is_gram) { prefetch_tmap(&map_m_hi); prefetch_tmap(&map_m_lo); }
-    for (int s = 0; s < Cfg::STAGES; ++s) { mbar_init(full_bar + s, 1); mbar_init(empty_bar + s, 1); }
+    for (int s = 0; s < Cfg::STAGES; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(conv_bar + s, Cfg::CONV_WARPS);  // one arrival per converter warp
+      mbar_init(empty_bar + s, 1);
+    }
     mbar_init(tmem_full_bar, 1);
     fence_barrier_init();
   }
@@ -257,9 +271,11 @@ __global__ void __launch_bounds__(128, 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   pdl_launch_dependents();
-  pdl_wait();  // everything below reads what the prep kernel wrote
+  // What the prep kernel produces is needed late: Msym by the dS producer's B loads, the zeroed G and the
+  // ticket by the gram epilogue.  S itself is the caller's tensor, so the main loop of the gram units and
+  // the A loads of the dS units overlap the prep kernel (pdl_wait() at the points of use).
 
-  int it0, it1;  // k-block range (gram) / j-block range (dS)
+  int it0, it1;  // k-block range (gram) / node-block range (dS)
   if (is_gram) {
     it0 = unit * p.kb_per_gram;
     it1 = min(p.n_kb, it0 + p.kb_per_gram);
@@ -276,13 +292,14 @@ __global__ void __launch_bounds__(128, 1)
       mbar_wait(empty_bar + stage, phase ^ 1);
       uint8_t* st = tiles + stage * Cfg::STAGE_BYTES;
       if (is_gram) {
-        mbar_expect_tx(full_bar + stage, 2 * Cfg::B_BYTES);
-        tma_load_2d(st + 2 * Cfg::A_BYTES, &map_s_hi, full_bar + stage, it * Cfg::BK, 0);
-        tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &map_s_lo, full_bar + stage, it * Cfg::BK, 0);
+        mbar_expect_tx(full_bar + stage, Cfg::B_BYTES);
+        tma_load_2d(st + 2 * Cfg::A_BYTES, &map_s_gram, full_bar + stage, it * Cfg::BK, 0);
       } else {
-        mbar_expect_tx(full_bar + stage, 2 * Cfg::A_BYTES + 2 * Cfg::B_BYTES);
-        tma_load_2d(st, &map_st_hi, full_bar + stage, it * Cfg::BK, unit * 128);
-        tma_load_2d(st + Cfg::A_BYTES, &map_st_lo, full_bar + stage, it * Cfg::BK, unit * 128);
+        mbar_expect_tx(full_bar + stage, Cfg::A_BYTES + 2 * Cfg::B_BYTES);
+#pragma unroll
+        for (int c = 0; c < 4; ++c)  // [32 node rows][32 columns] boxes: chunk c of the 128 columns
+          tma_load_2d(st + c * 4096, &map_s_ds, full_bar + stage, unit * 128 + c * 32, it * Cfg::BK);
+        if (it == it0) pdl_wait();  // Msym tiles come from the prep kernel
         tma_load_2d(st + 2 * Cfg::A_BYTES, &map_m_hi, full_bar + stage, it * Cfg::BK, 0);
         tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &map_m_lo, full_bar + stage, it * Cfg::BK, 0);
       }
@@ -290,41 +307,74 @@ __global__ void __launch_bounds__(128, 1)
     }
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer (one thread) =====
-    constexpr uint32_t idesc = make_idesc_tf32(128, NPAD);
+    constexpr uint32_t idesc_gram = make_idesc_tf32(128, NPAD, false);
+    constexpr uint32_t idesc_ds = make_idesc_tf32(128, NPAD, true);
     int stage = 0;
     uint32_t phase = 0;
     for (int it = it0; it < it1; ++it) {
-      mbar_wait(full_bar + stage, phase);
+      mbar_wait(conv_bar + stage, phase);
       tc_fence_after();
       const uint32_t st = smem_u32(tiles + stage * Cfg::STAGE_BYTES);
       const uint32_t b_hi = st + 2 * Cfg::A_BYTES, b_lo = b_hi + Cfg::B_BYTES;
-      {
-        const uint32_t a_hi = is_gram ? b_hi + mblk * Cfg::A_BYTES : st;
-        const uint32_t a_lo = is_gram ? b_lo + mblk * Cfg::A_BYTES : st + Cfg::A_BYTES;
-        const uint32_t d_tmem = tmem_base;
+      const uint32_t d_tmem = tmem_base;
+      if (is_gram) {
+        const uint32_t a_hi = b_hi + mblk * Cfg::A_BYTES, a_lo = b_lo + mblk * Cfg::A_BYTES;
 #pragma unroll
         for (int k4 = 0; k4 < Cfg::BK / 8; ++k4) {
           const uint64_t adh = make_kmajor_sw128_desc(a_hi) + 2 * k4, adl = make_kmajor_sw128_desc(a_lo) + 2 * k4;
           const uint64_t bdh = make_kmajor_sw128_desc(b_hi) + 2 * k4, bdl = make_kmajor_sw128_desc(b_lo) + 2 * k4;
-          umma_tf32(d_tmem, adh, bdh, idesc, (it > it0 || k4 > 0) ? 1u : 0u);
-          umma_tf32(d_tmem, adh, bdl, idesc, 1u);
-          umma_tf32(d_tmem, adl, bdh, idesc, 1u);
+          umma_tf32(d_tmem, adh, bdh, idesc_gram, (it > it0 || k4 > 0) ? 1u : 0u);
+          umma_tf32(d_tmem, adh, bdl, idesc_gram, 1u);
+          umma_tf32(d_tmem, adl, bdh, idesc_gram, 1u);
+        }
+      } else {
+        const uint32_t a_hi = st, a_lo = st + Cfg::A_BYTES;
+#pragma unroll
+        for (int k4 = 0; k4 < Cfg::BK / 8; ++k4) {
+          const uint64_t adh = make_mnmajor_sw128_desc(a_hi) + 64 * k4, adl = make_mnmajor_sw128_desc(a_lo) + 64 * k4;
+          const uint64_t bdh = make_kmajor_sw128_desc(b_hi) + 2 * k4, bdl = make_kmajor_sw128_desc(b_lo) + 2 * k4;
+          umma_tf32(d_tmem, adh, bdh, idesc_ds, (it > it0 || k4 > 0) ? 1u : 0u);
+          umma_tf32(d_tmem, adh, bdl, idesc_ds, 1u);
+          umma_tf32(d_tmem, adl, bdh, idesc_ds, 1u);
         }
       }
       umma_commit(empty_bar + stage);  // frees the smem slot once these MMAs have read it
       if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
     }
     umma_commit(tmem_full_bar);
+  } else if (warp >= 2) {
+    // ===== converters: raw f32 tile -> remainder tile (the raw tile itself serves as the tf32 head:
+    // the tensor core reads only the top 19 bits of a tf32 operand) =====
+    const int ctid = threadIdx.x - 64;
+    const int n_chunks = (is_gram ? Cfg::B_BYTES : Cfg::A_BYTES) / 16;
+    const int lo_off = is_gram ? Cfg::B_BYTES : Cfg::A_BYTES;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int it = it0; it < it1; ++it) {
+      mbar_wait(full_bar + stage, phase);
+      uint8_t* raw = tiles + stage * Cfg::STAGE_BYTES + (is_gram ? 2 * Cfg::A_BYTES : 0);
+#pragma unroll 4
+      for (int c = ctid; c < n_chunks; c += 32 * Cfg::CONV_WARPS) {
+        const float4 x = *reinterpret_cast<const float4*>(raw + (size_t)c * 16);
+        *reinterpret_cast<float4*>(raw + lo_off + (size_t)c * 16) =
+            make_float4(x.x - tf32_hi(x.x), x.y - tf32_hi(x.y), x.z - tf32_hi(x.z), x.w - tf32_hi(x.w));
+      }
+      fence_proxy_async();  // make the generic-proxy writes visible to tcgen05.mma (async proxy)
+      __syncwarp();
+      if (lane == 0) mbar_arrive(conv_bar + stage);
+      if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+    }
   }
   __syncwarp();
 
-  // ===== epilogue: all four warps, warp w owns TMEM lanes 32w .. 32w+31 =====
-  mbar_wait(tmem_full_bar, 0);
-  tc_fence_after();
-  const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-  if (is_gram) {
-    // partial G of this split-K slice -> G with 128-bit fire-and-forget reductions (no slabs)
-    {
+  // ===== epilogue: warps 0-3, warp w owns TMEM lanes 32w .. 32w+31 =====
+  if (warp < 4) {
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
+    if (is_gram) {
+      // partial G of this split-K slice -> G with 128-bit fire-and-forget reductions
+      pdl_wait();  // G was zeroed (and the ticket reset) by the prep kernel
       float* row = p.g + (size_t)(mblk * 128 + warp * 32 + lane) * NPAD;
 #pragma unroll 1
       for (int c0 = 0; c0 < NPAD; c0 += 32) {
@@ -336,23 +386,76 @@ __global__ void __launch_bounds__(128, 1)
                        "f"(v[q + 2]), "f"(v[q + 3])
                        : "memory");
       }
-    }
-  } else {
-    const long long kcol = (long long)unit * 128 + warp * 32 + lane;
+    } else {
+      const long long kcol = (long long)unit * 128 + warp * 32 + lane;
 #pragma unroll 1
-    for (int c0 = 0; c0 < NPAD; c0 += 32) {
-      float v[32];
-      tmem_ld32(tmem_base + lane_base + c0, v);
-      if (kcol < p.k) {
+      for (int c0 = 0; c0 < NPAD; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_base + lane_base + c0, v);
+        if (kcol < p.k) {
 #pragma unroll
-        for (int q = 0; q < 32; ++q)
-          if (c0 + q < p.n_nodes) p.d_seqs[(size_t)(c0 + q) * p.k + kcol] = v[q];
+          for (int q = 0; q < 32; ++q)
+            if (c0 + q < p.n_nodes) p.d_seqs[(size_t)(c0 + q) * p.k + kcol] = v[q];
+        }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+
+  // ===== fused finalisation: cost = <M, G>, dAdj_ij = (G_ii + G_jj)/2 - G_ij =====
+  // Every gram CTA takes a ticket after its reductions into G; the last one sees the complete G
+  // (release: __threadfence before the ticket; acquire: __threadfence after it, G read past L1).
+  if (p.fuse_final && is_gram) {
+    __shared__ bool s_last;
+    __shared__ double s_red[Cfg::THREADS / 32];
+    if (threadIdx.x == 0) {
+      __threadfence();
+      s_last = atomicAdd(p.ticket, 1u) == (unsigned)(p.n_gram * Cfg::MBLK - 1);
+      __threadfence();
+    }
+    __syncthreads();
+    if (s_last) {
+      const int N = p.n_nodes;  // <= 64 on this path (run())
+      __shared__ float s_diag[128], s_dd[128];
+      if (threadIdx.x < N) {
+        s_diag[threadIdx.x] = __ldcg(p.g + (size_t)threadIdx.x * NPAD + threadIdx.x);
+        s_dd[threadIdx.x] = __ldcg(p.d + threadIdx.x);
+      }
+      __syncthreads();
+      double part = 0.0;
+      constexpr int U = 8;  // independent loads in flight per thread: the pass is L2-latency bound
+      for (int base = threadIdx.x; base < N * N; base += Cfg::THREADS * U) {
+        float g[U], a[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int e = base + u * Cfg::THREADS;
+          const int i = e / N, j = e - i * N;
+          g[u] = e < N * N ? __ldcg(p.g + (size_t)i * NPAD + j) : 0.f;
+          a[u] = e < N * N ? __ldg(p.adj + e) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int e = base + u * Cfg::THREADS;
+          if (e < N * N) {
+            const int i = e / N, j = e - i * N;
+            part += ((i == j ? (double)s_dd[i] : 0.0) - (double)a[u]) * (double)g[u];
+            if (p.d_adj) p.d_adj[e] = 0.5f * (s_diag[i] + s_diag[j]) - g[u];
+          }
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (lane == 0) s_red[warp] = part;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int q = 0; q < Cfg::THREADS / 32; ++q) t += s_red[q];
+        *p.out_cost = (float)t;
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -394,33 +497,25 @@ __global__ void __launch_bounds__(256)
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 static int pad_nodes(int n) { return n <= 128 ? 128 : 256; }
-static long long pad_k(long long k) { return (k + 127) / 128 * 128; }
 
 static void plan_split(long long k, int& n_kb, int& kb_per, int& n_gram) {
   n_kb = (int)((k + 31) / 32);
   kb_per = (n_kb + kMaxSlabs - 1) / kMaxSlabs;
-  if (kb_per < 4) kb_per = 4;
+  if (kb_per < 2) kb_per = 2;
   n_gram = (n_kb + kb_per - 1) / kb_per;
 }
 
-static TcBuffers carve(void* ws, int n_nodes, long long k) {
+static TcBuffers carve(void* ws, int n_nodes) {
   TcBuffers w{};
   w.npad = pad_nodes(n_nodes);
-  w.kp = pad_k(k);
-  int n_kb, kb_per;
-  plan_split(k, n_kb, kb_per, w.n_slabs);
   char* p = (char*)ws;
   auto take = [&](size_t bytes) { char* r = p; p += align256(bytes); return r; };
   w.cost = (double*)take(8);
   w.ticket = (unsigned*)take(4);
   w.d = (float*)take(sizeof(float) * kMaxNodes);
-  const size_t nn = sizeof(float) * (size_t)w.npad * w.npad, nk = sizeof(float) * (size_t)w.npad * w.kp;
+  const size_t nn = sizeof(float) * (size_t)w.npad * w.npad;
   w.m_hi = (float*)take(nn);
   w.m_lo = (float*)take(nn);
-  w.s_hi = (float*)take(nk);
-  w.s_lo = (float*)take(nk);
-  w.st_hi = (float*)take(nk);
-  w.st_lo = (float*)take(nk);
   w.g = (float*)take(nn);
   return w;
 }
@@ -428,20 +523,18 @@ static TcBuffers carve(void* ws, int n_nodes, long long k) {
 size_t workspace_bytes(int n_nodes, long long k) {
   if (n_nodes < 1 || n_nodes > kMaxNodes || k < 1) return 0;
   const int npad = pad_nodes(n_nodes);
-  const long long kp = pad_k(k);
-  int n_kb, kb_per, n_gram;
-  plan_split(k, n_kb, kb_per, n_gram);
-  const size_t nn = align256(sizeof(float) * (size_t)npad * npad), nk = align256(sizeof(float) * (size_t)npad * kp);
-  (void)n_gram;
-  return 256 * 2 + align256(sizeof(float) * kMaxNodes) + 3 * nn + 4 * nk + 256;
+  const size_t nn = align256(sizeof(float) * (size_t)npad * npad);
+  return 256 * 2 + align256(sizeof(float) * kMaxNodes) + 3 * nn + 256;
 }
 
-bool supported(int n_nodes, int cost_kind) {
+bool supported(const float* seqs, int n_nodes, long long k, int cost_kind) {
   // TREX_TREE_COST_PATH=simt keeps the exact-f32 CUDA-core path (parity baseline); read per call so
-  // tests can exercise both paths in one process
+  // tests can exercise both paths in one process.  TMA reads S in place: base and row pitch must be
+  // multiples of 16 bytes.
   const char* e = getenv("TREX_TREE_COST_PATH");
   const bool forced_simt = e && e[0] == 's';
-  return !forced_simt && cost_kind == 0 && n_nodes >= 1 && n_nodes <= kMaxNodes;
+  return !forced_simt && cost_kind == 0 && n_nodes >= 1 && n_nodes <= kMaxNodes && k % 4 == 0 &&
+         (reinterpret_cast<uintptr_t>(seqs) & 15) == 0;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -460,8 +553,10 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// row-major f32 [rows][cols] with `pitch` floats per row; box = box_rows x 32 floats, 128B swizzle
-static int make_map(CUtensorMap* map, float* base, long long rows, long long cols, long long pitch, int box_rows) {
+// row-major f32 [rows][cols] with `pitch` floats per row; box = box_rows x 32 floats, 128B swizzle;
+// elements outside [rows][cols] read as zero
+static int make_map(CUtensorMap* map, const float* base, long long rows, long long cols, long long pitch, int box_rows,
+                    CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_error("tree_cost(tcgen05): cuTensorMapEncodeTiled is not available from the driver");
@@ -471,8 +566,8 @@ static int make_map(CUtensorMap* map, float* base, long long rows, long long col
   cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(float)};
   cuuint32_t box[2] = {32u, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1u, 1u};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("tree_cost(tcgen05): cuTensorMapEncodeTiled failed (%d)", (int)r);
     return TREX_ERR_CUDA;
@@ -497,31 +592,28 @@ static cudaLaunchConfig_t pdl_config(dim3 grid, dim3 block, size_t smem, cudaStr
 }
 
 template <int NPAD>
-static int launch_gemm(const TcBuffers& w, const GemmParams& gp, cudaStream_t stream) {
-  CUtensorMap ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo;
+static int launch_gemm(const float* seqs, const TcBuffers& w, const GemmParams& gp, cudaStream_t stream) {
+  CUtensorMap ms_gram, ms_ds, mm_hi, mm_lo;
   int rc;
-  if ((rc = make_map(&ms_hi, w.s_hi, NPAD, w.kp, w.kp, NPAD))) return rc;
-  if ((rc = make_map(&ms_lo, w.s_lo, NPAD, w.kp, w.kp, NPAD))) return rc;
-  if ((rc = make_map(&mst_hi, w.st_hi, w.kp, NPAD, NPAD, 128))) return rc;
-  if ((rc = make_map(&mst_lo, w.st_lo, w.kp, NPAD, NPAD, 128))) return rc;
+  if ((rc = make_map(&ms_gram, seqs, gp.n_nodes, gp.k, gp.k, NPAD))) return rc;  // [Npad rows][32 cols]
+  if ((rc = make_map(&ms_ds, seqs, gp.n_nodes, gp.k, gp.k, 32, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B))) return rc;  // [32 rows][32 cols], MN-major operand
   if ((rc = make_map(&mm_hi, w.m_hi, NPAD, NPAD, NPAD, NPAD))) return rc;
   if ((rc = make_map(&mm_lo, w.m_lo, NPAD, NPAD, NPAD, NPAD))) return rc;
   auto kern = tc_gemm_kernel<NPAD>;
   rc = check_cuda(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, GemmCfg<NPAD>::SMEM_BYTES),
                   "cudaFuncSetAttribute(tc_gemm_kernel)");
   if (rc) return rc;
-  cudaLaunchConfig_t cfg = pdl_config(dim3(gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds), dim3(128), GemmCfg<NPAD>::SMEM_BYTES, stream);
-  rc = check_cuda(cudaLaunchKernelEx(&cfg, kern, ms_hi, ms_lo, mst_hi, mst_lo, mm_hi, mm_lo, gp), "tc_gemm_kernel");
+  cudaLaunchConfig_t cfg = pdl_config(dim3(gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds), dim3(GemmCfg<NPAD>::THREADS),
+                                      GemmCfg<NPAD>::SMEM_BYTES, stream);
+  rc = check_cuda(cudaLaunchKernelEx(&cfg, kern, ms_gram, ms_ds, mm_hi, mm_lo, gp), "tc_gemm_kernel");
   note_launches(1);
   return rc;
 }
 
 int run(const float* seqs, const float* adj, int n_nodes, long long k, float* out_cost, float* d_seqs, float* d_adj,
         void* workspace, cudaStream_t stream) {
-  TcBuffers w = carve(workspace, n_nodes, k);
-  const long long tiles = (long long)(w.npad / 32) * (w.kp / 32);
-  TREX_CHECK_ARG(w.npad + tiles <= 2147483647LL, "tree_cost(tcgen05): K too large");
-  prep_kernel<<<(unsigned)(w.npad + tiles), 256, 0, stream>>>(seqs, adj, n_nodes, k, w);
+  TcBuffers w = carve(workspace, n_nodes);
+  prep_kernel<<<w.npad, 256, 0, stream>>>(adj, n_nodes, w);
   note_launches(1);
   TREX_CHECK_LAUNCH("tc::prep_kernel");
   GemmParams gp{};
@@ -531,8 +623,15 @@ int run(const float* seqs, const float* adj, int n_nodes, long long k, float* ou
   gp.n_ds = d_seqs ? (int)((k + 127) / 128) : 0;
   gp.g = w.g;
   gp.d_seqs = d_seqs;
-  int rc = w.npad == 128 ? launch_gemm<128>(w, gp, stream) : launch_gemm<256>(w, gp, stream);
-  if (rc) return rc;
+  // small trees are latency-bound: the last gram CTA finalises in place and the third kernel is skipped
+  gp.fuse_final = n_nodes <= 64 ? 1 : 0;  // beyond that one CTA's N^2 pass costs more than a launch
+  gp.adj = adj;
+  gp.d = w.d;
+  gp.ticket = w.ticket;
+  gp.out_cost = out_cost;
+  gp.d_adj = d_adj;
+  int rc = w.npad == 128 ? launch_gemm<128>(seqs, w, gp, stream) : launch_gemm<256>(seqs, w, gp, stream);
+  if (rc || gp.fuse_final) return rc;
   cudaLaunchConfig_t cfg = pdl_config(dim3(n_nodes), dim3(256), 0, stream);
   rc = check_cuda(cudaLaunchKernelEx(&cfg, final_kernel, adj, n_nodes, w, out_cost, d_adj), "tc::final_kernel");
   note_launches(1);

@@ -10,22 +10,17 @@ constexpr int kMaxSlabs = 64;    // split-K slices of the Gram contraction
 
 struct TcBuffers {
   int npad;            // 128 or 256
-  long long kp;        // K rounded up to 128 (row pitch of S_hi / S_lo, rows of ST_*)
-  int n_slabs;
   float* d;            // [N] (rowsum + colsum) / 2
   double* cost;        // [1]
   unsigned* ticket;    // [1]
-  float* m_hi;         // [npad][npad]  M + M^T
-  float* m_lo;
-  float* s_hi;         // [npad][kp]
-  float* s_lo;
-  float* st_hi;        // [kp][npad]
-  float* st_lo;
+  float* m_hi;         // [npad][npad]  M + M^T, tf32 head
+  float* m_lo;         //               and exact remainder
   float* g;            // [npad][npad] G = S S^T (f32, reduced with red.global.add)
 };
 
 size_t workspace_bytes(int n_nodes, long long k);
-bool supported(int n_nodes, int cost_kind);
+// identity cost, N <= kMaxNodes, and S addressable by TMA (16-byte aligned base and row pitch)
+bool supported(const float* seqs, int n_nodes, long long k, int cost_kind);
 // value + gradients for cost_kind == 0; d_seqs / d_adj may be null
 int run(const float* seqs, const float* adj, int n_nodes, long long k, float* out_cost, float* d_seqs,
         float* d_adj, void* workspace, cudaStream_t stream);
