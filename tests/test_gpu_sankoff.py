@@ -237,3 +237,46 @@ def test_full_size_properties(n, A, L):
   assert np.array_equal(edge, fitch)  # the reconstruction realises the optimal score
   hist = eng.edge_hist[0].cpu().numpy()
   assert hist.sum() == (n_all - 1) * L and hist.sum() - np.trace(hist) == fitch.sum()
+
+
+@pytest.mark.parametrize("kind,n", [("balanced", 1024), ("random", 300), ("cat", 64), ("balanced", 4), ("random", 2)])
+def test_plan_segments_partition_the_post_order(kind, n):
+  """The plan's subtree decomposition (common.cuh: PlanView / Walk): segments are disjoint contiguous
+  runs of the post-order, each closed under taking children; the top list holds every other node in
+  post-order; together they cover each internal node exactly once."""
+  torch = _torch()
+  from trex_b200.sankoff import SankoffEngine
+
+  adj, _, _, _ = _case(kind, n, 4, 8, seed=n)
+  n_all, n_int = 2 * n - 1, n - 1
+  eng = SankoffEngine(n_all, n, 4, 8)
+  eng.set_adjacency(torch.from_numpy(adj))
+  plan = eng.plan[0].cpu().numpy()
+  hdr, body = plan[:8], plan[8:]
+  ch = [body[0:n_int], body[n_int:2 * n_int]]
+  order = body[4 * n_int:5 * n_int]
+  top = body[7 * n_int:8 * n_int]
+  seg_start, seg_len = body[8 * n_int:8 * n_int + 64], body[8 * n_int + 64:8 * n_int + 128]
+  n_reach, n_seg, n_top_reach, n_top = int(hdr[1]), int(hdr[2]), int(hdr[4]), int(hdr[5])
+  assert n_reach == n_int and sorted(order.tolist()) == list(range(n, n_all))
+  pos = {int(v): i for i, v in enumerate(order)}
+  for k in range(n_int):  # post-order: children before parents
+    for c in (ch[0][k], ch[1][k]):
+      if c >= n:
+        assert pos[int(c)] < pos[n + k]
+  covered = []
+  for s in range(n_seg):
+    run = order[seg_start[s]:seg_start[s] + seg_len[s]].tolist()
+    members = set(run)
+    for v in run:  # closed under children, and the run's last node is the only one with an outside parent
+      for c in (ch[0][v - n], ch[1][v - n]):
+        if c >= n:
+          assert int(c) in members
+    covered += run
+  assert len(covered) == len(set(covered))
+  assert n_top == n_top_reach == n_int - len(covered)
+  assert sorted(covered + top[:n_top].tolist()) == list(range(n, n_all))
+  tpos = [pos[int(v)] for v in top[:n_top]]
+  assert tpos == sorted(tpos)
+  if n >= 64 and kind == "balanced":
+    assert n_seg >= 16  # enough independent subtrees to fill the machine on short alignments

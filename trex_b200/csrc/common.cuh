@@ -10,6 +10,8 @@ namespace trex {
 
 constexpr float kSentinel = 1e5f;  // src/trex/sankoff.py:152
 constexpr int kPlanHdr = 8;        // int32 header words per tree plan
+constexpr int kMaxSeg = 64;        // independent subtrees ("segments") a plan can expose
+constexpr int kSegTarget = 32;     // the builder aims at this many segments of ~n_reach / kSegTarget nodes
 
 // plan word offsets (per tree); n_int = n_all - n_leaves
 struct PlanView {
@@ -20,12 +22,49 @@ struct PlanView {
   __device__ const int32_t* child(int k) const { return base + kPlanHdr + k * n_int; }      // k=0,1
   __device__ const int32_t* raw(int k) const { return base + kPlanHdr + (2 + k) * n_int; }  // k=0,1
   __device__ const int32_t* order() const { return base + kPlanHdr + 4 * n_int; }
+  // Subtree decomposition for short alignments (few sites -> few warps): maximal subtrees of at most
+  // ~n_reach / kSegTarget internal nodes are contiguous runs order[seg_start .. +seg_len) of the
+  // post-order and independent of each other; top_order lists the remaining nodes in post-order
+  // (reachable ones first, hdr[4] of them; hdr[5] in total with the nodes the root does not reach).
+  __device__ const int32_t* top_order() const { return base + kPlanHdr + 7 * n_int; }
+  __device__ const int32_t* seg_start() const { return base + kPlanHdr + 8 * n_int; }
+  __device__ const int32_t* seg_len() const { return base + kPlanHdr + 8 * n_int + kMaxSeg; }
 };
+
+// The node list one kernel launch walks.  phase 0: the whole tree (order, all n_int nodes forward /
+// the n_reach reachable ones in reverse); phase 1: segment `z` of the plan; phase 2: the top part.
+struct Walk {
+  const int32_t* ord;
+  int n_fwd;  // nodes a forward (post-order) walk visits
+  int n_rev;  // nodes a reverse walk visits: ord[n_rev-1] down to ord[0]
+};
+__device__ __forceinline__ Walk make_walk(const PlanView& plan, int phase, int z) {
+  Walk w;
+  const int32_t* h = plan.hdr();
+  if (phase == 0) {
+    w.ord = plan.order();
+    w.n_fwd = plan.n_int;
+    w.n_rev = h[1];
+  } else if (phase == 1) {
+    const bool on = z < h[2];
+    w.ord = plan.order() + (on ? plan.seg_start()[z] : 0);
+    w.n_fwd = w.n_rev = on ? plan.seg_len()[z] : 0;
+  } else {
+    w.ord = plan.top_order();
+    w.n_fwd = h[5];
+    w.n_rev = h[4];
+  }
+  return w;
+}
 
 void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 int sm_count();
 void note_launches(int n);  // process-wide count of kernel launches (trex_kernel_launches)
+// Short alignments expose too few site blocks to fill the GPU: walk the plan's independent subtrees in
+// parallel (two launches: segments, then the top part).  n_site_warps = warps of site work per pass.
+// TREX_SEGMENTS=0/1 forces the choice (tests).
+bool use_segments(long long n_site_warps);
 
 #define TREX_CHECK_ARG(cond, ...)        \
   do {                                   \

@@ -17,6 +17,7 @@ struct HardFwdParams {
   float* root_min;
   double* total;
   int mode;
+  int phase;  // node list of this launch (common.cuh: Walk): 0 whole tree, 1 segment blockIdx.z, 2 top part
 };
 
 struct SoftFwdParams {
@@ -30,6 +31,7 @@ struct SoftFwdParams {
   float T;
   float* dp;
   double* total;
+  int phase;  // as HardFwdParams::phase
 };
 
 // Uniform substitution cost: C[s][s] == 0 and C[s][t] == a >= 0 for every s != t (Fitch-style

@@ -135,6 +135,11 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
   const int tree = blockIdx.y;
   const int n_int = p.n_all - p.n_leaves;
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+  const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+  const int n_walk = wk.n_fwd;
+  if (n_walk == 0) return;
+  // the root is the last reachable node of the walk that contains it
+  const bool has_root = wk.n_rev > 0 && __ldg(wk.ord + wk.n_rev - 1) == p.n_all - 1;
   const size_t stride = (size_t)p.stride;
   const long long site0 = ((long long)blockIdx.x * THREADS + threadIdx.x) * V;
   const bool active = site0 < p.n_sites;
@@ -146,7 +151,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
     float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
     uint8_t* arg = WANT_ARG ? p.arg + (size_t)tree * n_int * 2 * A * stride + site0 : nullptr;
     const uint8_t* leaf = p.leaf + site0;
-    const int32_t* order = plan.order();
+    const int32_t* order = wk.ord;
     const int32_t* ch0 = plan.child(0);
     const int32_t* ch1 = plan.child(1);
     // In DFS post-order the node computed last is a child of the next node: its row stays in
@@ -172,11 +177,11 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
       if (!fwd && cx >= 0 && cx < p.n_leaves) ld_u8<V>(leaf + (size_t)cx * stride, ox);
       if (cy >= 0 && cy < p.n_leaves) ld_u8<V>(leaf + (size_t)cy * stride, oy);
     };
-    if (n_int > 0) {
+    {
       decode(0);
       if (cy >= p.n_leaves) load_rows<AP, V, FULL>(dp + (size_t)(cy - p.n_leaves) * A * stride, A, stride, dy);
     }
-    for (int i = 0; i < n_int; ++i) {
+    for (int i = 0; i < n_walk; ++i) {
       if (!fwd) {
         if (cx >= p.n_leaves) load_rows<AP, V, FULL>(dp + (size_t)(cx - p.n_leaves) * A * stride, A, stride, dx);
         else leaf_rows<AP, V, FULL>(ox, A, dx);
@@ -197,7 +202,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
       }
       // the next node (its leaf states are fetched now, its dy rows inside the state loop)
       prev = node;
-      const bool more = i + 1 < n_int;
+      const bool more = i + 1 < n_walk;
       if (more) decode(i + 1);
       const bool reload = more && cy >= p.n_leaves;
       const float* nsrc = dp + (size_t)(reload ? cy - p.n_leaves : 0) * A * stride;
@@ -222,19 +227,19 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
           if (reload) ld_f<V>(nsrc + (size_t)s * stride, dy[s]);
         }
       });
-    }
-    // per-site root minimum (sankoff.py:187): the root is the last node, its row is in dx
-    if (prev == p.n_all - 1) {
+      // per-site root minimum (sankoff.py:187); nodes the root does not reach may still follow
+      if (prev == p.n_all - 1) {
 #pragma unroll
-      for (int s = 0; s < AP; ++s)
-        if (FULL || s < A) {
+        for (int s = 0; s < AP; ++s)
+          if (FULL || s < A) {
 #pragma unroll
-          for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], dx[s][v]);
-        }
+            for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], dx[s][v]);
+          }
+      }
     }
-    if (p.root_min) st_f<V>(p.root_min + (size_t)tree * stride + site0, rmin);
+    if (p.root_min && has_root) st_f<V>(p.root_min + (size_t)tree * stride + site0, rmin);
   }
-  if (p.total) {
+  if (p.total && has_root) {
     double acc = 0.0;
     if (active) {
 #pragma unroll
@@ -283,6 +288,10 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
   const int tree = blockIdx.y;
   const int n_int = p.n_all - p.n_leaves;
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+  const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+  const int n_walk = wk.n_fwd;
+  if (n_walk == 0) return;
+  const bool has_root = wk.n_rev > 0 && __ldg(wk.ord + wk.n_rev - 1) == p.n_all - 1;
   const float c1 = 1.4426950408889634f / p.T;    // log2(e)/T
   const float tln2 = p.T * 0.6931471805599453f;  // T*ln(2)
   const float kk = exp2f(-a * c1);               // exp(-a/T)
@@ -295,7 +304,7 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
     float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
     const uint8_t* leaf = p.leaf ? p.leaf + site0 : nullptr;
     const float* leaf_cost = p.leaf_cost ? p.leaf_cost + site0 : nullptr;
-    const int32_t* order = plan.order();
+    const int32_t* order = wk.ord;
     const int32_t* ch0 = plan.child(0);
     const int32_t* ch1 = plan.child(1);
     // rows of a child that lives in memory (dp node, or a leaf of a float leaf-cost table); null for
@@ -325,11 +334,11 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
       if (!fwd && !sx && cx >= 0 && leaf) ld_u8<V>(leaf + (size_t)cx * stride, ox);
       if (!sy && cy >= 0 && leaf) ld_u8<V>(leaf + (size_t)cy * stride, oy);
     };
-    if (n_int > 0) {
+    {
       decode(0);
       if (sy) load_rows<AP, V, FULL>(sy, A, stride, dy);
     }
-    for (int i = 0; i < n_int; ++i) {
+    for (int i = 0; i < n_walk; ++i) {
       if (!fwd) {
         if (sx) load_rows<AP, V, FULL>(sx, A, stride, dx);
         else leaf_rows<AP, V, FULL>(ox, A, dx);
@@ -343,7 +352,7 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
       for (int v = 0; v < V; ++v) mxy[v] = mx[v] + my[v];
       float* out = dp + (size_t)k * A * stride;
       prev = node;
-      const bool more = i + 1 < n_int;
+      const bool more = i + 1 < n_walk;
       if (more) decode(i + 1);
       const bool reload = more && sy != nullptr;
       const float* nsrc = reload ? sy : dp;
@@ -366,7 +375,7 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
     }
     // total += softmin_s dp[root][s]   (sankoff.py:187 relaxed); the root row is in dx when it was
     // the last node of the plan
-    if (n_int > 0) {
+    if (has_root) {
       if (prev != p.n_all - 1) load_rows<AP, V, FULL>(dp + (size_t)(n_int - 1) * A * stride, A, stride, dx);
 #pragma unroll
       for (int v = 0; v < V; ++v) {
@@ -382,21 +391,32 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
       }
     }
   }
-  if (p.total) block_atomic_add(acc, p.total + tree);
+  if (p.total && has_root) block_atomic_add(acc, p.total + tree);
 }
 
 namespace {
 template <int AP, int V>
-void launch_hard_uniform(const HardFwdParams& p, int batch, cudaStream_t s) {
+void launch_hard_uniform(const HardFwdParams& p0, int batch, cudaStream_t s) {
   constexpr int T = 128;
-  const dim3 grid((unsigned)((p.n_sites + (long long)T * V - 1) / ((long long)T * V)), batch);
-  const bool full = p.n_states == AP;
-  if (p.arg) {
-    if (full) { hard_fwd_uniform_kernel<AP, V, T, true, true><<<grid, T, 0, s>>>(p); note_launches(1); }
-    else { hard_fwd_uniform_kernel<AP, V, T, false, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+  const unsigned gx = (unsigned)((p0.n_sites + (long long)T * V - 1) / ((long long)T * V));
+  const bool full = p0.n_states == AP;
+  auto run = [&](const HardFwdParams& p, dim3 grid) {
+    if (p.arg) {
+      if (full) { hard_fwd_uniform_kernel<AP, V, T, true, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+      else { hard_fwd_uniform_kernel<AP, V, T, false, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+    } else {
+      if (full) { hard_fwd_uniform_kernel<AP, V, T, true, false><<<grid, T, 0, s>>>(p); note_launches(1); }
+      else { hard_fwd_uniform_kernel<AP, V, T, false, false><<<grid, T, 0, s>>>(p); note_launches(1); }
+    }
+  };
+  if (use_segments((long long)gx * (T / 32) * batch)) {
+    HardFwdParams p = p0;
+    p.phase = 1;  // independent subtrees side by side ...
+    run(p, dim3(gx, batch, kMaxSeg));
+    p.phase = 2;  // ... then the nodes above them
+    run(p, dim3(gx, batch));
   } else {
-    if (full) { hard_fwd_uniform_kernel<AP, V, T, true, false><<<grid, T, 0, s>>>(p); note_launches(1); }
-    else { hard_fwd_uniform_kernel<AP, V, T, false, false><<<grid, T, 0, s>>>(p); note_launches(1); }
+    run(p0, dim3(gx, batch));
   }
 }
 }  // namespace
@@ -412,11 +432,22 @@ int launch_hard_fwd_uniform(const HardFwdParams& p, int batch, cudaStream_t s) {
 
 namespace {
 template <int AP, int V>
-void launch_soft_uniform(const SoftFwdParams& p, int batch, cudaStream_t s) {
+void launch_soft_uniform(const SoftFwdParams& p0, int batch, cudaStream_t s) {
   constexpr int T = 128;
-  const dim3 grid((unsigned)((p.n_sites + (long long)T * V - 1) / ((long long)T * V)), batch);
-  if (p.n_states == AP) { soft_fwd_uniform_kernel<AP, V, T, true><<<grid, T, 0, s>>>(p); note_launches(1); }
-  else { soft_fwd_uniform_kernel<AP, V, T, false><<<grid, T, 0, s>>>(p); note_launches(1); }
+  const unsigned gx = (unsigned)((p0.n_sites + (long long)T * V - 1) / ((long long)T * V));
+  auto run = [&](const SoftFwdParams& p, dim3 grid) {
+    if (p.n_states == AP) { soft_fwd_uniform_kernel<AP, V, T, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+    else { soft_fwd_uniform_kernel<AP, V, T, false><<<grid, T, 0, s>>>(p); note_launches(1); }
+  };
+  if (use_segments((long long)gx * (T / 32) * batch)) {
+    SoftFwdParams p = p0;
+    p.phase = 1;
+    run(p, dim3(gx, batch, kMaxSeg));
+    p.phase = 2;
+    run(p, dim3(gx, batch));
+  } else {
+    run(p0, dim3(gx, batch));
+  }
 }
 }  // namespace
 
