@@ -33,6 +33,7 @@ struct TraceParams {
   const uint8_t* arg;
   uint8_t* anc;
   unsigned long long* hist;
+  int phase;  // node list of this launch (common.cuh: Walk): 0 whole tree, 1 segment blockIdx.z, 2 top part
 };
 
 template <int V, int THREADS>
@@ -52,16 +53,18 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
     const uint8_t* arg = p.arg + (size_t)tree * n_int * 2 * A * p.stride + site0;
     uint8_t* anc = p.anc + (size_t)tree * n_int * p.stride + site0;
     const uint8_t* leaf = p.leaf + site0;
-    const int32_t* order = plan.order();
-    const int n_reach = plan.hdr()[1];
-    // nodes the root does not reach keep the reference's zero initialisation (sankoff.py:215)
-    int zero[V];
+    const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+    const int32_t* order = wk.ord;
+    const int n_reach = wk.n_rev;
+    const bool has_root = n_reach > 0 && __ldg(order + n_reach - 1) == p.n_all - 1;
+    if (has_root) {
+      // nodes the root does not reach keep the reference's zero initialisation (sankoff.py:215)
+      int zero[V];
 #pragma unroll
-    for (int v = 0; v < V; ++v) zero[v] = 0;
-    for (int i = n_reach; i < n_int; ++i)
-      st_u8<V>(anc + (size_t)(__ldg(order + i) - p.n_leaves) * p.stride, zero);
-    // root state: first argmin of the root row (sankoff.py:172)
-    {
+      for (int v = 0; v < V; ++v) zero[v] = 0;
+      for (int i = plan.hdr()[1]; i < n_int; ++i)
+        st_u8<V>(anc + (size_t)(__ldg(plan.order() + i) - p.n_leaves) * p.stride, zero);
+      // root state: first argmin of the root row (sankoff.py:172)
       const int k = n_int - 1;
       float best[V];
       int st[V];
@@ -243,9 +246,17 @@ int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_s
   // One site per lane: the walk is a chain of dependent one-byte gathers, so resident warps (latency
   // hiding) matter more than vector width; measured 1.78 -> 1.29 ms at c5 against V = 4.
   constexpr int V = 1;
-  dim3 grid((unsigned)(((n_sites + V - 1) / V + THREADS - 1) / THREADS), batch);
-  traceback_kernel<V, THREADS><<<grid, THREADS, smem, s>>>(p);
-  note_launches(1);
+  const unsigned gx = (unsigned)(((n_sites + V - 1) / V + THREADS - 1) / THREADS);
+  if (use_segments((long long)gx * (THREADS / 32) * batch)) {
+    p.phase = 2;  // top-down: the nodes above the segments first, then the independent subtrees
+    traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
+    p.phase = 1;
+    traceback_kernel<V, THREADS><<<dim3(gx, batch, kMaxSeg), THREADS, smem, s>>>(p);
+    note_launches(2);
+  } else {
+    traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
+    note_launches(1);
+  }
   TREX_CHECK_LAUNCH("traceback_kernel");
   return TREX_OK;
 }

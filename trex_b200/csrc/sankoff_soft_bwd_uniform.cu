@@ -130,10 +130,13 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
   float* gbar = p.gbar + (size_t)tree * n_int * A * stride + site0;
   float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * stride + site0 : nullptr;
   const float* leaf_cost = p.leaf_cost ? p.leaf_cost + site0 : nullptr;
-  const int32_t* order = plan.order();
+  const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+  const int32_t* order = wk.ord;  // this launch walks order[n_reach-1] down to order[0]
+  const int n_reach = wk.n_rev;
+  if (n_reach == 0) return;
+  const bool has_root = __ldg(order + n_reach - 1) == p.n_all - 1;  // the root is the last reachable node
   const int32_t* ch0 = plan.child(0);
   const int32_t* ch1 = plan.child(1);
-  const int n_reach = plan.hdr()[1];
   float* myG = sG + lane * V;  // this lane's column of the staged rows
   float* myR = sR + lane * V;
   float* myE = sE + lane * V;
@@ -186,20 +189,19 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
   };
 
   // ---- nodes the root does not reach get zero cotangent; root: gscale * softmax(-dp/T) --------
-  bool have_g = false;  // sG holds the cotangent of the node about to be processed
-  {
+  const bool have_g0 = has_root;  // sG holds the cotangent of the node about to be processed
+  if (has_root) {  // (the walk that owns the root)
     float zero[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) zero[v] = 0.f;
     if (active) {
-      for (int i = n_reach; i < n_int; ++i) {
-        float* row = gbar + (size_t)(__ldg(order + i) - p.n_leaves) * A * stride;
+      for (int i = plan.hdr()[1]; i < n_int; ++i) {
+        float* row = gbar + (size_t)(__ldg(plan.order() + i) - p.n_leaves) * A * stride;
         for (int s = 0; s < A; ++s) st_f<V>(row + s * stride, zero);
       }
     }
     const float* rrow = dp + (size_t)(n_int - 1) * A * stride;
     float* grow = gbar + (size_t)(n_int - 1) * A * stride;
-    have_g = n_reach > 0 && __ldg(order + n_reach - 1) == p.n_all - 1;
     float mm[V], z[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) { mm[v] = INFINITY; z[v] = 0.f; }
@@ -227,6 +229,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
     }
   }
 
+  bool have_g = have_g0;
   float d[AP][V];  // dp row of the next child with a cost row (prefetched), e in place once used
   const float* pf_src = nullptr;
 
@@ -487,15 +490,28 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
 
 namespace {
 template <int AP, int V>
-int launch_uniform(const SoftBwdParams& p, int batch, cudaStream_t s) {
+int launch_uniform(const SoftBwdParams& p0, int batch, cudaStream_t s) {
   using Cfg = UniCfg<AP, V>;
   const size_t smem = sizeof(float) * (size_t)Cfg::kWarpFloats;
-  dim3 grid((unsigned)((p.n_sites + Cfg::NS - 1) / Cfg::NS), batch);
+  const unsigned gx = (unsigned)((p0.n_sites + Cfg::NS - 1) / Cfg::NS);
+  const bool segs = use_segments((long long)gx * batch);
   auto go = [&](auto kern) -> cudaError_t {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess) { kern<<<grid, 32, smem, s>>>(p); note_launches(1); }
+    if (e != cudaSuccess) return e;
+    SoftBwdParams p = p0;
+    if (segs) {
+      p.phase = 2;  // the nodes above the segments first (root downwards) ...
+      kern<<<dim3(gx, batch), 32, smem, s>>>(p);
+      p.phase = 1;  // ... then the independent subtrees side by side
+      kern<<<dim3(gx, batch, kMaxSeg), 32, smem, s>>>(p);
+      note_launches(2);
+    } else {
+      kern<<<dim3(gx, batch), 32, smem, s>>>(p);
+      note_launches(1);
+    }
     return e;
   };
+  const SoftBwdParams& p = p0;
   const bool full = p.n_states == AP;
   cudaError_t e;
   if (p.dcost) e = full ? go(soft_bwd_uniform_kernel<AP, V, true, true>) : go(soft_bwd_uniform_kernel<AP, V, true, false>);

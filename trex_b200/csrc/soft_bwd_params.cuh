@@ -20,6 +20,7 @@ struct SoftBwdParams {
   float* dleaf;
   double* dcost;
   int only_direct;  // 1: return immediately when the exp-domain (warp-autonomous) kernel applies
+  int phase;        // node list of this launch (common.cuh: Walk): 0 whole tree, 1 segment blockIdx.z, 2 top part
 };
 
 // exp-domain evaluation is valid while exp(-C/T) cannot underflow a whole row sum
