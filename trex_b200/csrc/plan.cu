@@ -71,11 +71,18 @@ __global__ void __launch_bounds__(kColsPerCta* kRowChunks)
     const int rows_per = (n_all + kRowChunks - 1) / kRowChunks;
     const int r0 = r * rows_per;
     const int r1 = min(n_all, r0 + rows_per);
-    for (int i = r0; i < r1 && f1 < 0; ++i) {
-      float v = __ldg(a + (size_t)i * n_all + col);
-      if (zero_root_selfloop && i == n_all - 1 && col == n_all - 1) v = 0.f;  // sankoff.py:141
-      if (v == 1.0f) {
-        if (f0 < 0) f0 = i; else f1 = i;
+    // eight independent loads in flight per thread (the scan is latency-bound); stop after the second hit
+    for (int i0 = r0; i0 < r1 && f1 < 0; i0 += 8) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = i0 + u < r1 ? __ldg(a + (size_t)(i0 + u) * n_all + col) : 0.f;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + u;
+        if (zero_root_selfloop && i == n_all - 1 && col == n_all - 1) v[u] = 0.f;  // sankoff.py:141
+        if (v[u] == 1.0f && f1 < 0) {
+          if (f0 < 0) f0 = i; else f1 = i;
+        }
       }
     }
   }
@@ -103,15 +110,19 @@ __global__ void __launch_bounds__(kColsPerCta* kRowChunks)
 }
 
 // ---- kernel 2: DFS post-order, subtree segments (one CTA per tree) ---------------------------
-// The passes are sequential (thread 0) but run on shared-memory copies of the child arrays when the
-// tree fits (n_int <= kSmemNodes), which takes the dependent-load latency from ~L2 to ~30 cycles per
-// node; larger trees use the global arrays directly.  Two linear passes, no stack.
-constexpr int kSmemNodes = 8192;  // 5 int32 arrays of this many nodes = 160 KB of dynamic shared memory
+// Works on shared-memory copies of the per-node arrays when the tree fits (n_int <= kSmemNodes),
+// directly on the plan's global arrays otherwise.  Subtree sizes are propagated bottom-up and post-order
+// offsets top-down in parallel rounds (one round per tree level, all threads of the CTA; a balanced
+// 1024-leaf tree takes 10 + 10 rounds instead of two 1023-step dependent chains); the few inherently
+// ordered steps (numbering the segments, compacting the top list) are light single-thread loops.
+constexpr int kSmemNodes = 8192;  // 6 int32 arrays of this many nodes = 192 KB of dynamic shared memory
+constexpr int kPlanThreads = 256;
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kPlanThreads)
     plan_order_kernel(int n_all, int n_leaves, int32_t* __restrict__ plan, size_t plan_words, int use_smem) {
   extern __shared__ int32_t sm[];
   const int n_int = n_all - n_leaves;
+  const int tid = threadIdx.x;
   int32_t* p = plan + (size_t)blockIdx.x * plan_words;
   int32_t* g_ch0 = p + kPlanHdr;
   int32_t* g_ch1 = p + kPlanHdr + n_int;
@@ -123,122 +134,182 @@ __global__ void __launch_bounds__(256)
   const int32_t* ch0 = g_ch0;
   const int32_t* ch1 = g_ch1;
   int32_t *order = g_order, *size = g_size, *off = g_off;
+  int32_t* par = p + kPlanHdr + 8 * n_int + 2 * kMaxSeg;  // parent (internal index) or -1; later: in-segment map
   if (use_smem) {
     int32_t* s0 = sm;
     int32_t* s1 = sm + n_int;
-    for (int k = threadIdx.x; k < n_int; k += blockDim.x) { s0[k] = g_ch0[k]; s1[k] = g_ch1[k]; }
+    for (int k = tid; k < n_int; k += kPlanThreads) { s0[k] = g_ch0[k]; s1[k] = g_ch1[k]; }
     ch0 = s0;
     ch1 = s1;
     order = sm + 2 * n_int;
     size = sm + 3 * n_int;
     off = sm + 4 * n_int;
-    __syncthreads();
+    par = sm + 5 * n_int;
   }
   __shared__ int s_hdr[8];
-  if (threadIdx.x == 0) {
-    int status = 0;
-    for (int k = 0; k < n_int; ++k) off[k] = -1;
-    // pass 1 (ascending): subtree sizes in internal nodes; detect shared children / sentinels
-    for (int k = 0; k < n_int; ++k) {
+  __shared__ int s_status;
+  if (tid == 0) s_status = 0;
+  for (int k = tid; k < n_int; k += kPlanThreads) { size[k] = 0; off[k] = -1; par[k] = -1; }
+  __syncthreads();
+  // parents; shared children / sentinel children
+  for (int k = tid; k < n_int; k += kPlanThreads) {
+    const int a = ch0[k], b = ch1[k];
+    int st = 0;
+    if (a < 0 || b < 0) st |= TREX_PLAN_HAS_SENTINEL_CHILD;
+    if (a >= n_leaves && atomicExch(&par[a - n_leaves], k) != -1) st |= TREX_PLAN_NOT_A_TREE;
+    if (b >= n_leaves && atomicExch(&par[b - n_leaves], k) != -1) st |= TREX_PLAN_NOT_A_TREE;
+    if (st) atomicOr(&s_status, st);
+  }
+  __syncthreads();
+  // bottom-up rounds: a node's size is known once its internal children's are (children have smaller
+  // indices, so this terminates; also valid on a DAG)
+  for (;;) {
+    int changed = 0;
+    for (int k = tid; k < n_int; k += kPlanThreads) {
+      if (size[k]) continue;
       const int a = ch0[k], b = ch1[k];
-      int s = 1;
-      if (a < 0 || b < 0) status |= TREX_PLAN_HAS_SENTINEL_CHILD;
-      if (a >= n_leaves) {
-        s += size[a - n_leaves];
-        if (off[a - n_leaves] == -2) status |= TREX_PLAN_NOT_A_TREE;
-        off[a - n_leaves] = -2;
-      }
-      if (b >= n_leaves) {
-        s += size[b - n_leaves];
-        if (off[b - n_leaves] == -2) status |= TREX_PLAN_NOT_A_TREE;
-        off[b - n_leaves] = -2;
-      }
-      size[k] = s;
+      const int sa = a >= n_leaves ? size[a - n_leaves] : -1, sb = b >= n_leaves ? size[b - n_leaves] : -1;
+      if (sa == 0 || sb == 0) continue;
+      size[k] = 1 + (sa > 0 ? sa : 0) + (sb > 0 ? sb : 0);
+      changed = 1;
     }
-    int n_reach = 0, n_seg = 0, n_top_reach = 0, n_top = 0;
-    if (!(status & TREX_PLAN_NOT_A_TREE)) {
-      for (int k = 0; k < n_int; ++k) off[k] = -1;
-      // pass 2 (descending): post-order offsets; the larger internal subtree goes first so the
-      // number of rows waiting for their sibling stays small (they are re-read from L2).
-      // Segments: a node whose subtree has at most `cap` internal nodes while its parent's has more
-      // roots a segment (its whole subtree is the contiguous run order[off .. off + size)).  `off`
-      // of a node inside a segment is flagged by adding kInSeg to its parent's decision below.
-      n_reach = size[n_int - 1];
-      const int cap = max(1, (n_reach + kSegTarget - 1) / kSegTarget);
-      int next = 0;
-      for (int k = n_int - 1; k >= 0; --k) {
+    if (!__syncthreads_or(changed)) break;
+  }
+  const int status = s_status;
+  if (!(status & TREX_PLAN_NOT_A_TREE)) {
+    const int n_reach = size[n_int - 1];
+    const int cap = max(1, (n_reach + kSegTarget - 1) / kSegTarget);
+    // offsets of the forest roots: the root first (its subtree is order[0 .. n_reach)); roots the root
+    // does not reach take disjoint ranges behind it (any order is valid for them)
+    __shared__ int s_next;
+    if (tid == 0) { s_next = n_reach; off[n_int - 1] = 0; }
+    __syncthreads();
+    for (int k = tid; k < n_int - 1; k += kPlanThreads)
+      if (par[k] < 0) off[k] = atomicAdd(&s_next, size[k]);
+    // top-down rounds: a node with a known offset places itself and hands offsets to its children; the
+    // larger internal subtree goes first so that few rows wait for their sibling (re-read from L2).
+    // order[] doubles as the "expanded" marker: it is filled exactly once per node.
+    for (int k = tid; k < n_int; k += kPlanThreads) order[k] = -1;
+    __syncthreads();
+    for (;;) {
+      int changed = 0;
+      for (int k = tid; k < n_int; k += kPlanThreads) {
         int o = off[k];
-        bool in_seg = false;
-        if (o <= -4) {  // parent already belongs to a segment: encoded offset
-          in_seg = true;
-          o = -o - 4;
-        } else if (o < 0) {  // not reached from a parent: a root of the forest
-          o = next;
-          next += size[k];
-        }
-        const bool reach = o < n_reach;  // the root's subtree occupies order[0 .. n_reach)
-        if (!in_seg && reach && size[k] <= cap && n_seg < kMaxSeg && n_reach > 1) {
-          g_seg[n_seg] = o;
-          g_seg[kMaxSeg + n_seg] = size[k];
-          ++n_seg;
-          in_seg = true;
-        }
+        if (o < 0 || order[o + size[k] - 1] == n_leaves + k) continue;
         order[o + size[k] - 1] = n_leaves + k;
-        if (in_seg) size[k] = -size[k];  // sign = "inside a segment" (restored below)
         int a = ch0[k] >= n_leaves ? ch0[k] - n_leaves : -1;
         int b = ch1[k] >= n_leaves ? ch1[k] - n_leaves : -1;
         if (a >= 0 && b >= 0 && size[b] > size[a]) {
           const int t = a; a = b; b = t;
         }
         if (a >= 0) {
-          off[a] = in_seg ? -(o + 4) : o;
+          off[a] = o;
           o += size[a];
         }
-        if (b >= 0) off[b] = in_seg ? -(o + 4) : o;
+        if (b >= 0) off[b] = o;
+        changed = 1;
       }
-      // top part: every node outside the segments, in post-order (= ascending position in `order`):
-      // reachable ones first, then the nodes the root does not reach (forward walks still fill them)
-      for (int i = 0; i < n_int; ++i) {
-        const int k = order[i] - n_leaves;
-        if (size[k] > 0) {
-          g_top[n_top++] = order[i];
-          if (i < n_reach) ++n_top_reach;
-        }
-      }
-      for (int k = 0; k < n_int; ++k) {
-        size[k] = size[k] < 0 ? -size[k] : size[k];
-        off[k] = off[k] <= -4 ? -off[k] - 4 : off[k];
-      }
-    } else {
-      // fallback: plain index order (always valid for the forward); reachable nodes first; no segments
-      for (int k = 0; k < n_int; ++k) off[k] = 0;
-      off[n_int - 1] = 1;
-      for (int k = n_int - 1; k >= 0; --k) {
-        if (!off[k]) continue;
-        ++n_reach;
-        if (ch0[k] >= n_leaves) off[ch0[k] - n_leaves] = 1;
-        if (ch1[k] >= n_leaves) off[ch1[k] - n_leaves] = 1;
-      }
-      int w0 = 0, w1 = n_reach;
-      for (int k = 0; k < n_int; ++k) {
-        if (off[k]) order[w0++] = n_leaves + k; else order[w1++] = n_leaves + k;
-      }
-      for (int i = 0; i < n_int; ++i) g_top[i] = order[i];
-      n_top = n_int;
-      n_top_reach = n_reach;
+      if (!__syncthreads_or(changed)) break;
     }
-    s_hdr[0] = n_int;
+    // Ordered compactions over post-order positions (thread t owns a contiguous chunk of positions;
+    // chunk counts are combined with a block-wide exclusive scan).
+    __shared__ int s_scan[kPlanThreads];
+    const int chunk = (n_int + kPlanThreads - 1) / kPlanThreads;
+    const int i_lo = min(n_int, tid * chunk), i_hi = min(n_int, i_lo + chunk);
+    auto block_exclusive = [&](int count, int& total) -> int {
+      s_scan[tid] = count;
+      __syncthreads();
+      for (int d = 1; d < kPlanThreads; d <<= 1) {
+        const int v = tid >= d ? s_scan[tid - d] : 0;
+        __syncthreads();
+        s_scan[tid] += v;
+        __syncthreads();
+      }
+      total = s_scan[kPlanThreads - 1];
+      const int excl = s_scan[tid] - count;
+      __syncthreads();
+      return excl;
+    };
+    // segments: maximal subtrees of at most `cap` internal nodes inside the root's subtree, numbered by
+    // position; at most kMaxSeg (later ones stay in the top part)
+    auto is_seg_root = [&](int i) {
+      if (n_reach <= 1 || i >= n_reach) return false;
+      const int k = order[i] - n_leaves;
+      return size[k] <= cap && (par[k] < 0 || size[par[k]] > cap);
+    };
+    int cnt = 0;
+    for (int i = i_lo; i < i_hi; ++i) cnt += is_seg_root(i) ? 1 : 0;
+    int total_seg;
+    int idx = block_exclusive(cnt, total_seg);
+    for (int i = i_lo; i < i_hi; ++i) {
+      if (!is_seg_root(i)) continue;
+      if (idx < kMaxSeg) {
+        const int k = order[i] - n_leaves;
+        g_seg[idx] = off[k];
+        g_seg[kMaxSeg + idx] = size[k];
+      }
+      ++idx;
+    }
+    const int n_seg = min(total_seg, kMaxSeg);
+    __syncthreads();
+    // par[] is no longer needed: reuse it as the "position is inside a segment" map
+    for (int k = tid; k < n_int; k += kPlanThreads) par[k] = 0;
+    __syncthreads();
+    for (int sgi = tid / 32; sgi < n_seg; sgi += kPlanThreads / 32) {  // one warp per segment
+      const int s0 = g_seg[sgi], l0 = g_seg[kMaxSeg + sgi];
+      for (int i = tid % 32; i < l0; i += 32) par[s0 + i] = 1;
+    }
+    __syncthreads();
+    // top part: every node outside the segments in post-order, reachable ones first
+    cnt = 0;
+    int cnt_reach = 0;
+    for (int i = i_lo; i < i_hi; ++i) {
+      if (par[i]) continue;
+      ++cnt;
+      if (i < n_reach) ++cnt_reach;
+    }
+    int n_top, n_top_reach;
+    idx = block_exclusive(cnt, n_top);
+    (void)block_exclusive(cnt_reach, n_top_reach);
+    for (int i = i_lo; i < i_hi; ++i)
+      if (!par[i]) g_top[idx++] = order[i];
+    if (tid == 0) {
+      s_hdr[1] = n_reach;
+      s_hdr[2] = n_seg;
+      s_hdr[4] = n_top_reach;
+      s_hdr[5] = n_top;
+    }
+  } else if (tid == 0) {
+    // not a tree (a child with two parents): plain index order (always valid for the forward walk),
+    // reachable nodes first; no segments
+    int n_reach = 0;
+    for (int k = 0; k < n_int; ++k) off[k] = 0;
+    off[n_int - 1] = 1;
+    for (int k = n_int - 1; k >= 0; --k) {
+      if (!off[k]) continue;
+      ++n_reach;
+      if (ch0[k] >= n_leaves) off[ch0[k] - n_leaves] = 1;
+      if (ch1[k] >= n_leaves) off[ch1[k] - n_leaves] = 1;
+    }
+    int w0 = 0, w1 = n_reach;
+    for (int k = 0; k < n_int; ++k) {
+      if (off[k]) order[w0++] = n_leaves + k; else order[w1++] = n_leaves + k;
+    }
+    for (int i = 0; i < n_int; ++i) g_top[i] = order[i];
     s_hdr[1] = n_reach;
-    s_hdr[2] = n_seg;
+    s_hdr[2] = 0;
+    s_hdr[4] = n_reach;
+    s_hdr[5] = n_int;
+  }
+  if (tid == 0) {
+    s_hdr[0] = n_int;
     s_hdr[3] = status;
-    s_hdr[4] = n_top_reach;
-    s_hdr[5] = n_top;
     s_hdr[6] = s_hdr[7] = 0;
   }
   __syncthreads();
-  if (threadIdx.x < 8) p[threadIdx.x] = s_hdr[threadIdx.x];
+  if (tid < 8) p[tid] = s_hdr[tid];
   if (use_smem) {
-    for (int k = threadIdx.x; k < n_int; k += blockDim.x) {
+    for (int k = tid; k < n_int; k += kPlanThreads) {
       g_order[k] = order[k];
       g_size[k] = size[k];
       g_off[k] = off[k];
@@ -257,7 +328,7 @@ unsigned long long trex_kernel_launches(void) { return trex::kernel_launches(); 
 size_t trex_sankoff_plan_words(int n_all, int n_leaves) {
   const int n_int = n_all - n_leaves;
   if (n_int < 0) return 0;
-  return (size_t)trex::kPlanHdr + 8 * (size_t)n_int + 2 * (size_t)trex::kMaxSeg;
+  return (size_t)trex::kPlanHdr + 9 * (size_t)n_int + 2 * (size_t)trex::kMaxSeg;  // (+ n_int words of builder scratch)
 }
 
 int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
@@ -275,13 +346,13 @@ int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
   note_launches(1);
   TREX_CHECK_LAUNCH("plan_children_kernel");
   const int use_smem = n_int <= kSmemNodes;
-  const size_t smem = use_smem ? 5 * sizeof(int32_t) * (size_t)n_int : 0;
+  const size_t smem = use_smem ? 6 * sizeof(int32_t) * (size_t)n_int : 0;
   if (smem > 48 * 1024) {
     int rc = check_cuda(cudaFuncSetAttribute(plan_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                         "cudaFuncSetAttribute(plan_order_kernel)");
     if (rc) return rc;
   }
-  plan_order_kernel<<<batch, 256, smem, s>>>(n_all, n_leaves, plan, words, use_smem);
+  plan_order_kernel<<<batch, kPlanThreads, smem, s>>>(n_all, n_leaves, plan, words, use_smem);
   note_launches(1);
   TREX_CHECK_LAUNCH("plan_order_kernel");
   return TREX_OK;
