@@ -280,3 +280,32 @@ def test_plan_segments_partition_the_post_order(kind, n):
   assert tpos == sorted(tpos)
   if n >= 64 and kind == "balanced":
     assert n_seg >= 16  # enough independent subtrees to fill the machine on short alignments
+
+
+@pytest.mark.parametrize("ck", ["unit", "int"])
+def test_internal_node_the_root_does_not_reach(ck):
+  """A forest: internal node 4 (child: leaf 3) hangs off nothing, the root 6 = (5, 2), 5 = (0, 1).  The
+  forward pass still fills node 4's row (the reference computes every node in index order) and the root
+  minimum must come from the root's row although node 4 follows the root in the plan's node list."""
+  torch = _torch()
+  from trex_b200.sankoff import SankoffEngine
+
+  n, A, L = 4, 5, 37
+  n_all = 2 * n - 1
+  adj = np.zeros((n_all, n_all), dtype=np.float32)
+  for c, par in [(0, 5), (1, 5), (5, 6), (2, 6), (3, 4)]:
+    adj[c, par] = 1
+  rng = np.random.default_rng(11)
+  states = rng.integers(0, A, size=(n, L)).astype(np.uint8)
+  cost = synth.unit_cost(A) if ck == "unit" else synth.random_int_cost(A, 4, rng)
+  tabs = so.run_sankoff_tables(adj, cost, states, n_all, A, n)
+  eng = SankoffEngine(n_all, n, A, L)
+  eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states))
+  eng.hard_forward(torch.from_numpy(cost))
+  dp, arg = _native_tables(eng)
+  assert np.array_equal(dp, tabs["dp"])
+  assert np.array_equal(eng.root_min[0, :L].cpu().numpy(), so.per_site_root_min(tabs["dp"]))
+  assert float(eng.total[0]) == float(so.per_site_root_min(tabs["dp"]).astype(np.float64).sum())
+  eng.traceback()
+  want = so.traceback_topdown(tabs, n_all, n)
+  assert np.array_equal(eng.anc[0, :, :L].cpu().numpy(), want[n:].astype(np.uint8))

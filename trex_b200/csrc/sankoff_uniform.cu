@@ -227,17 +227,19 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
           if (reload) ld_f<V>(nsrc + (size_t)s * stride, dy[s]);
         }
       });
-      // per-site root minimum (sankoff.py:187); nodes the root does not reach may still follow
-      if (prev == p.n_all - 1) {
-#pragma unroll
-        for (int s = 0; s < AP; ++s)
-          if (FULL || s < A) {
-#pragma unroll
-            for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], dx[s][v]);
-          }
-      }
     }
-    if (p.root_min && has_root) st_f<V>(p.root_min + (size_t)tree * stride + site0, rmin);
+    // per-site root minimum (sankoff.py:187): the root's row is still in dx unless nodes the root does
+    // not reach followed it in the walk
+    if (has_root) {
+      if (prev != p.n_all - 1) load_rows<AP, V, FULL>(dp + (size_t)(n_int - 1) * A * stride, A, stride, dx);
+#pragma unroll
+      for (int s = 0; s < AP; ++s)
+        if (FULL || s < A) {
+#pragma unroll
+          for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], dx[s][v]);
+        }
+      if (p.root_min) st_f<V>(p.root_min + (size_t)tree * stride + site0, rmin);
+    }
   }
   if (p.total && has_root) {
     double acc = 0.0;
