@@ -61,7 +61,10 @@ TREX_API unsigned long long trex_kernel_launches(void);
  * children of every internal node (first two rows equal to 1, ascending, -1 when missing)
  * and a DFS post-order in which a child's row is consumed right after it is produced.
  * `zero_root_selfloop` applies run_sankoff's `adj[-1,-1] = 0` (:141).  adj: [batch][n_all][n_all] f32.
- * plan: [batch][trex_sankoff_plan_words()] int32. */
+ * The plan also holds a decomposition into independent subtrees ("segments": contiguous runs of the
+ * post-order) plus the list of the nodes above them; on short alignments (too few sites to fill the
+ * GPU) the walk kernels process the segments side by side in one launch and the top part in a second.
+ * plan: [batch][trex_sankoff_plan_words()] int32 (opaque to the caller). */
 TREX_API size_t trex_sankoff_plan_words(int n_all, int n_leaves);
 TREX_API int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
                       int zero_root_selfloop, int32_t* plan, void* stream);
