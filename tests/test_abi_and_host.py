@@ -42,7 +42,7 @@ def test_library_exports_every_declared_symbol(lib):
 
 def test_host_side_queries_and_argument_errors(lib):
   assert lib.trex_version() >= 100
-  assert lib.trex_sankoff_plan_words(2047, 1024) == 8 + 9 * 1023 + 2 * 64  # header, 9 per-node arrays, segment table
+  assert lib.trex_sankoff_plan_words(2047, 1024) == 8 + 9 * 1023 + 2 * 128  # header, 9 per-node arrays, segment table
   assert lib.trex_tree_cost_workspace_bytes(127, 4000, 4) >= 127 * 127 * 8
   # null pointers / bad sizes are rejected on the host, before any CUDA call
   rc = lib.trex_sankoff_plan(None, 5, 3, 1, 1, None, None)

@@ -256,7 +256,7 @@ def test_plan_segments_partition_the_post_order(kind, n):
   ch = [body[0:n_int], body[n_int:2 * n_int]]
   order = body[4 * n_int:5 * n_int]
   top = body[7 * n_int:8 * n_int]
-  seg_start, seg_len = body[8 * n_int:8 * n_int + 64], body[8 * n_int + 64:8 * n_int + 128]
+  seg_start, seg_len = body[8 * n_int:8 * n_int + 128], body[8 * n_int + 128:8 * n_int + 256]
   n_reach, n_seg, n_top_reach, n_top = int(hdr[1]), int(hdr[2]), int(hdr[4]), int(hdr[5])
   assert n_reach == n_int and sorted(order.tolist()) == list(range(n, n_all))
   pos = {int(v): i for i, v in enumerate(order)}

@@ -31,10 +31,10 @@ static std::atomic<unsigned long long> g_kernel_launches{0};
 void note_launches(int n) { g_kernel_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 unsigned long long kernel_launches() { return g_kernel_launches.load(std::memory_order_relaxed); }
 
-bool use_segments(long long n_site_warps) {
+bool use_segments(int n_leaves) {
   const char* e = getenv("TREX_SEGMENTS");
   if (e && (e[0] == '0' || e[0] == '1')) return e[0] == '1';
-  return n_site_warps < 6LL * sm_count();
+  return n_leaves >= 64;
 }
 
 int sm_count() {
@@ -119,7 +119,8 @@ constexpr int kSmemNodes = 8192;  // 6 int32 arrays of this many nodes = 192 KB 
 constexpr int kPlanThreads = 256;
 
 __global__ void __launch_bounds__(kPlanThreads)
-    plan_order_kernel(int n_all, int n_leaves, int32_t* __restrict__ plan, size_t plan_words, int use_smem) {
+    plan_order_kernel(int n_all, int n_leaves, int32_t* __restrict__ plan, size_t plan_words, int use_smem,
+                      int seg_target) {
   extern __shared__ int32_t sm[];
   const int n_int = n_all - n_leaves;
   const int tid = threadIdx.x;
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(kPlanThreads)
   const int status = s_status;
   if (!(status & TREX_PLAN_NOT_A_TREE)) {
     const int n_reach = size[n_int - 1];
-    const int cap = max(1, (n_reach + kSegTarget - 1) / kSegTarget);
+    const int cap = max(1, (n_reach + seg_target - 1) / seg_target);
     // offsets of the forest roots: the root first (its subtree is order[0 .. n_reach)); roots the root
     // does not reach take disjoint ranges behind it (any order is valid for them)
     __shared__ int s_next;
@@ -352,7 +353,7 @@ int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
                         "cudaFuncSetAttribute(plan_order_kernel)");
     if (rc) return rc;
   }
-  plan_order_kernel<<<batch, kPlanThreads, smem, s>>>(n_all, n_leaves, plan, words, use_smem);
+  plan_order_kernel<<<batch, kPlanThreads, smem, s>>>(n_all, n_leaves, plan, words, use_smem, kSegTarget);
   note_launches(1);
   TREX_CHECK_LAUNCH("plan_order_kernel");
   return TREX_OK;

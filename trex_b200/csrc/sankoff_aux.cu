@@ -247,7 +247,7 @@ int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_s
   // hiding) matter more than vector width; measured 1.78 -> 1.29 ms at c5 against V = 4.
   constexpr int V = 1;
   const unsigned gx = (unsigned)(((n_sites + V - 1) / V + THREADS - 1) / THREADS);
-  if (use_segments((long long)gx * (THREADS / 32) * batch)) {
+  if (use_segments(n_leaves)) {
     p.phase = 2;  // top-down: the nodes above the segments first, then the independent subtrees
     traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
     p.phase = 1;

@@ -494,7 +494,7 @@ int launch_uniform(const SoftBwdParams& p0, int batch, cudaStream_t s) {
   using Cfg = UniCfg<AP, V>;
   const size_t smem = sizeof(float) * (size_t)Cfg::kWarpFloats;
   const unsigned gx = (unsigned)((p0.n_sites + Cfg::NS - 1) / Cfg::NS);
-  const bool segs = use_segments((long long)gx * batch);
+  const bool segs = use_segments(p0.n_leaves);
   auto go = [&](auto kern) -> cudaError_t {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;

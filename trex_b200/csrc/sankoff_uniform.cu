@@ -411,7 +411,7 @@ void launch_hard_uniform(const HardFwdParams& p0, int batch, cudaStream_t s) {
       else { hard_fwd_uniform_kernel<AP, V, T, false, false><<<grid, T, 0, s>>>(p); note_launches(1); }
     }
   };
-  if (use_segments((long long)gx * (T / 32) * batch)) {
+  if (use_segments(p0.n_leaves)) {
     HardFwdParams p = p0;
     p.phase = 1;  // independent subtrees side by side ...
     run(p, dim3(gx, batch, kMaxSeg));
@@ -441,7 +441,7 @@ void launch_soft_uniform(const SoftFwdParams& p0, int batch, cudaStream_t s) {
     if (p.n_states == AP) { soft_fwd_uniform_kernel<AP, V, T, true><<<grid, T, 0, s>>>(p); note_launches(1); }
     else { soft_fwd_uniform_kernel<AP, V, T, false><<<grid, T, 0, s>>>(p); note_launches(1); }
   };
-  if (use_segments((long long)gx * (T / 32) * batch)) {
+  if (use_segments(p0.n_leaves)) {
     SoftFwdParams p = p0;
     p.phase = 1;
     run(p, dim3(gx, batch, kMaxSeg));

@@ -95,7 +95,7 @@ def _soft_fwd(adj, cost, leaf_cost, n_leaves, n_sites, temperature):
   n_int = n_all - n_leaves
   return jax.ffi.ffi_call(
     "trex_soft_fwd_ffi",
-    (jax.ShapeDtypeStruct((8 + 9 * n_int + 128,), jnp.int32), jax.ShapeDtypeStruct((n_int, A, stride), jnp.float32),
+    (jax.ShapeDtypeStruct((8 + 9 * n_int + 256,), jnp.int32), jax.ShapeDtypeStruct((n_int, A, stride), jnp.float32),
      jax.ShapeDtypeStruct((1,), jnp.float64)),
     vmap_method="sequential",
   )(adj.astype(jnp.float32), cost.astype(jnp.float32), leaf_cost, n_leaves=jnp.int32(n_leaves),
