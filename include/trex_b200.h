@@ -185,6 +185,30 @@ TREX_API int trex_compute_cost(const float* seqs_one_hot, const float* adjacency
                       int n_nodes, int64_t n_sites, int n_states, int32_t* state_scratch,
                       int32_t* parent_scratch, double* acc_scratch, float* out_cost, void* stream);
 
+/* ---- whole ancestor-fitting loop on the device ------------------------------
+ * Replaces the body of run_trex_optimization_configurable (src/trex/evals/benchmark.py:75-200):
+ * n_iterations of { loss, grads = value_and_grad(loss_fn)(ancestors); optimizer.update; apply_updates }
+ * with loss_fn = compute_surrogate_cost(_update_seq_stacked(ancestors, masked_sequences, n_leaves, 1.0), adj)
+ * (:152-165; compute_soft_cost with the identity cost matrix is the same function) and
+ * optimizer = optax.chain(clip_by_global_norm(clip_norm), adam | sgd(momentum 0.9) | rmsprop | adamw(0.01))
+ * (create_optimizer, :41-72), as ONE persistent cooperative kernel (one grid barrier per iteration).
+ *   adjacency [N][N] f32 (any soft or hard adjacency); leaf_seqs [n_leaves][L][Q] f32 (one-hot or soft rows)
+ *   ancestor_logits [n_anc][L][Q] f32 in/out; opt_mom1 / opt_mom2 [n_anc][L][Q] f32 in/out (zeros at step 0):
+ *     first / second moment (adam, adamw), momentum trace in opt_mom1 (sgd), mean square in opt_mom2 (rmsprop)
+ *   optimizer: TREX_OPT_*; clip_norm <= 0 disables clipping; step_count = updates already applied (bias correction)
+ *   out_losses [n_iterations] f32 or NULL (loss BEFORE each update, as lax.scan returns them, :176-188)
+ *   out_argmax [n_anc][L] i32 or NULL (jnp.argmax(ancestors, -1) after the last update, :200)
+ *   workspace: trex_fit_ancestors_workspace_bytes(...) bytes.  n_anc <= 128 (else TREX_ERR_UNSUPPORTED). */
+#define TREX_OPT_ADAM 0
+#define TREX_OPT_SGD 1
+#define TREX_OPT_RMSPROP 2
+#define TREX_OPT_ADAMW 3
+TREX_API size_t trex_fit_ancestors_workspace_bytes(int n_nodes, int n_leaves, int64_t n_sites, int n_states);
+TREX_API int trex_fit_ancestors(const float* adjacency, const float* leaf_seqs, int n_nodes, int n_leaves,
+                       int64_t n_sites, int n_states, float* ancestor_logits, float* opt_mom1, float* opt_mom2,
+                       int optimizer, float learning_rate, float clip_norm, int n_iterations, int64_t step_count,
+                       float* out_losses, int32_t* out_argmax, void* workspace, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
