@@ -260,6 +260,74 @@ def tree_cost_bench(torch, iters=200):
                            "sample": "NumPy/BLAS float32 restatement of tree.py value+grad at c2"}}
 
 
+def fit_loop_bench(torch):
+  """the whole optimiser loop of run_trex_optimization_configurable
+  (evals/benchmark.py:75-200; adam + clip_by_global_norm(1.0), lr 1e-3, its defaults) as one persistent
+  kernel.  One "grad step" = loss value + gradient w.r.t. the ancestor logits + optimiser update.
+  device: CUDA events around one library call of `iters` iterations (setup kernels included);
+  e2e: host leaf states / adjacency / initial logits in pinned memory -> argmax + loss curve back on the host."""
+  from oracle import optimize_oracle as oo
+  from trex_b200 import optimize as O
+  from trex_b200 import synth
+
+  def one(n, L, Q, seed, iters):
+    rng = np.random.default_rng(seed)
+    parent = synth.balanced_parents(n)
+    N = parent.shape[0]
+    leaf = synth.evolve(parent, L, Q, 0.1, rng)[:n]
+    adj = synth.parents_to_adjacency(parent).astype(np.float32)
+    init = rng.normal(size=(N - n, L, Q)).astype(np.float32)
+    opt = O.create_optimizer("adam", 1e-3)
+    fit = O.AncestorFit(leaf, N, n, Q, adj, init, opt)
+    losses = torch.empty(iters, device="cuda")
+    fit.run(iters, losses)  # warm-up (module load, attribute set)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fit.run(iters, losses)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    # end to end through the reference-shaped call, host buffers in and out
+    leaf_p = torch.from_numpy(leaf.astype(np.int32)).pin_memory()
+    adj_p = torch.from_numpy(adj).pin_memory()
+    init_p = torch.from_numpy(init).pin_memory()
+    out_h = torch.empty((N - n, L), dtype=torch.int32).pin_memory()
+    loss_h = torch.empty(iters, dtype=torch.float32).pin_memory()
+    def e2e():
+      a, l = O.run_trex_optimization_configurable(
+        leaf_p.cuda(non_blocking=True), N, n, Q, adj_p.cuda(non_blocking=True), None, n_iterations=iters,
+        return_losses=True, init_ancestors=init_p.cuda(non_blocking=True))
+      out_h.copy_(a, non_blocking=True)
+      loss_h.copy_(l, non_blocking=True)
+    e2e()
+    torch.cuda.synchronize()
+    e0.record()
+    e2e()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = e0.elapsed_time(e1)
+    cpu_iters = 3
+    t0 = time.perf_counter()
+    oo.run_trex_optimization_configurable(leaf, N, n, Q, adj, init, "adam", 1e-3, cpu_iters, dtype=np.float32)
+    cpu_s = (time.perf_counter() - t0) / cpu_iters
+    return {"shape": f"{N} nodes ({n} leaves) x {L} sites x {Q} states, balanced tree, adam lr 1e-3 + clip 1.0",
+            "iterations": iters, "us_per_step": ms * 1e3 / iters, "grad_steps_per_s": iters / (ms * 1e-3),
+            "e2e_grad_steps_per_s": iters / (ms_e2e * 1e-3),
+            "e2e_h2d_bytes": int(leaf_p.numel() * 4 + adj_p.numel() * 4 + init_p.numel() * 4),
+            "e2e_d2h_bytes": int(out_h.numel() * 4 + loss_h.numel() * 4),
+            "final_loss": float(losses[-1]), "first_loss": float(losses[0]),
+            "cpu_grad_steps_per_s": 1.0 / cpu_s}
+
+  c2 = one(64, 1000, 4, 2, 10000)
+  q20 = one(100, 1000, 20, 242, 2000)
+  return {"metric": "fit_ancestors_grad_steps_per_s", "value": c2["grad_steps_per_s"], "unit": "grad steps/s",
+          "config": "c2: " + c2["shape"], "c2": c2, "script_q20": q20,
+          "path": "fit_ancestors_kernel: persistent cooperative kernel, 1 grid barrier per iteration, state resident in shared memory",
+          "cpu_baseline": {"value": c2["cpu_grad_steps_per_s"], "unit": "grad steps/s", "kind": "port",
+                           "sample": "3 iterations of the NumPy float32 restatement of the loop at c2 (optax/JAX absent)"}}
+
+
 def run_gpu(args):
   import torch
   import torch.distributed as dist
@@ -408,6 +476,7 @@ def run_gpu(args):
     }
     if world == 1 and not args.no_extras:
       line["tree_cost"] = tree_cost_bench(torch)
+      line["fit_loop"] = fit_loop_bench(torch)
       line["cpu_baseline"] = cpu_baseline(args.cpu_sites)
     emit(line)
   if world > 1:

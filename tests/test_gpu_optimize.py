@@ -30,13 +30,24 @@ SHAPES = [(64, 1000, 4, False), (8, 3001, 4, True), (16, 40000, 4, False), (4, 5
           (16, 333, 20, True), (128, 300, 4, False)]
 
 
+@pytest.fixture(params=["fast", "generic"])
+def kernel_path(request, monkeypatch):
+  """Q = 4 / 20 take the vectorised kernel (sparse or dense product); TREX_FIT_PATH=generic forces the
+  scalar any-Q kernel on the same inputs."""
+  if request.param == "generic":
+    monkeypatch.setenv("TREX_FIT_PATH", "generic")
+  else:
+    monkeypatch.delenv("TREX_FIT_PATH", raising=False)
+  return request.param
+
+
 @pytest.mark.parametrize("n,L,Q,soft", SHAPES)
-def test_loss_curve_and_logits_match_oracle(n, L, Q, soft):
+def test_loss_curve_and_logits_match_oracle(n, L, Q, soft, kernel_path):
   import torch
   from oracle import optimize_oracle as oo
   from trex_b200 import optimize as O
 
-  leaf, N, adj, init = _problem(n, L, Q, 10 + n)
+  leaf, N, adj, init = _problem(n, L, Q, 10 + n, soft_adj=soft)
   iters = 6 if L * n > 200000 else 12
   ref_arg, ref_losses, ref_x = oo.run_trex_optimization_configurable(leaf, N, n, Q, adj, init, "adam", 0.05, iters)
   fit = O.AncestorFit(leaf, N, n, Q, adj, init, O.create_optimizer("adam", 0.05))
@@ -54,7 +65,7 @@ def test_loss_curve_and_logits_match_oracle(n, L, Q, soft):
 
 
 @pytest.mark.parametrize("name", ["adam", "sgd", "rmsprop", "adamw"])
-def test_each_optimizer_matches_oracle(name):
+def test_each_optimizer_matches_oracle(name, kernel_path):
   import torch
   from oracle import optimize_oracle as oo
   from trex_b200 import optimize as O
@@ -71,7 +82,7 @@ def test_each_optimizer_matches_oracle(name):
   assert np.linalg.norm(x - ref_x) <= 2e-4 * np.linalg.norm(ref_x - init)
 
 
-def test_no_clipping_and_continuation():
+def test_no_clipping_and_continuation(kernel_path):
   import torch
   from oracle import optimize_oracle as oo
   from trex_b200 import optimize as O

@@ -16,47 +16,15 @@
 //    clip factor everywhere, run-to-run deterministic);
 //  * softmax, the product, the softmax VJP, the clip and the optimiser update never leave the SM.
 #include <algorithm>
+#include <cstdlib>
 
-#include "common.cuh"
+#include "fit_ancestors.cuh"
 
 namespace trex {
 
+using namespace fit;
+
 namespace {
-
-constexpr int kThreads = 256;
-constexpr int kMaxAnc = 128;   // A2[anc, anc] lives in shared memory
-constexpr int kTileCols = 64;  // columns (sites x states) of one product tile
-
-enum { OPT_ADAM = 0, OPT_SGD = 1, OPT_RMSPROP = 2, OPT_ADAMW = 3 };
-
-struct FitParams {
-  const float* a2;    // [N][N]
-  const float* bias;  // B [n_anc][K]
-  const double* c0;
-  float* theta;       // [n_anc][K] logits, in/out
-  float* mom1;        // [n_anc][K] first moment (adam, adamw) / trace (sgd); unused by rmsprop
-  float* mom2;        // [n_anc][K] second moment (adam, adamw, rmsprop); unused by sgd
-  float* grad;        // [n_anc][K] scratch (only touched when the state is not shared-memory resident)
-  float* losses;      // [n_iter] or null
-  int32_t* argmax;    // [n_anc][L] or null
-  double* slots;      // [2][grid][2]
-  unsigned long long* bar;
-  int N, n_leaves, n_anc, Q;
-  long long L, K;
-  int opt;
-  float lr, clip, weight_decay;
-  int n_iter;
-  long long count0;
-  int sites_per_cta;
-  int tile_sites;
-  int resident;
-};
-
-__device__ __forceinline__ unsigned long long ld_acquire(const unsigned long long* p) {
-  unsigned long long v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
 
 // fixed-order block sum of two doubles (every thread gets the result)
 __device__ __forceinline__ void block_sum2(double& a, double& b, double* red /* [2][kThreads/32] */) {
@@ -107,6 +75,26 @@ __global__ void fit_bias_kernel(const float* __restrict__ a2, const float* __res
     else part = 0.5 * (double)acc * (double)s_leaf[(size_t)row * K + col];
   }
   if (row < n_leaves) block_atomic_add(part, c0);
+}
+
+// ELL form of A2[anc, anc]: a hard tree has at most 4 non-zeros per row (diagonal, parent, two children)
+__global__ void fit_ell_kernel(const float* __restrict__ a2, int N, int n_leaves, int32_t* __restrict__ idx,
+                               float* __restrict__ val, int32_t* __restrict__ ok) {
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n_anc = N - n_leaves;
+  if (a >= n_anc) return;
+  const float* row = a2 + (size_t)(n_leaves + a) * N + n_leaves;
+  int k = 0;
+  bool fits = true;
+  for (int b = 0; b < n_anc; ++b) {
+    const float v = row[b];
+    if (v != 0.f) {
+      if (k < kEll) { idx[a * kEll + k] = b; val[a * kEll + k] = v; ++k; }
+      else fits = false;
+    }
+  }
+  for (; k < kEll; ++k) { idx[a * kEll + k] = -1; val[a * kEll + k] = 0.f; }
+  if (!fits) *ok = 0;
 }
 
 // ---- the loop --------------------------------------------------------------------------------
@@ -216,7 +204,7 @@ __global__ void __launch_bounds__(kThreads) fit_ancestors_kernel(const FitParams
       const int tc4 = (tcols + 3) >> 2;
       const int cbase = s0 * Q;
       // softmax of the logits (temperature 1: _update_seq_stacked, evals/benchmark.py:231)
-      for (int i = threadIdx.x; i < n_anc * ts; i += kThreads) {
+      for (int i = threadIdx.x; i < ((p.debug & 8) ? 0 : n_anc * ts); i += kThreads) {
         const int a = i / ts, s = i - a * ts;
         const float* x = th + (size_t)a * ld + cbase + s * Q;
         float* out = sS + a * ldt + s * Q;
@@ -235,12 +223,13 @@ __global__ void __launch_bounds__(kThreads) fit_ancestors_kernel(const FitParams
         }
       __syncthreads();
       const int RT4 = (n_anc + 3) >> 2;
-      if (RT4 * tc4 >= kThreads * 3 / 4) product_tile<4>(sA, lda, sS, sD, ldt, n_anc, tc4, bi + cbase, (int)ld, tcols);
+      if (p.debug & 2) {}
+      else if (RT4 * tc4 >= kThreads * 3 / 4) product_tile<4>(sA, lda, sS, sD, ldt, n_anc, tc4, bi + cbase, (int)ld, tcols);
       else product_tile<2>(sA, lda, sS, sD, ldt, n_anc, tc4, bi + cbase, (int)ld, tcols);
       __syncthreads();
       // softmax VJP, the loss and |g|^2
       float fc = 0.f, fn = 0.f;
-      for (int i = threadIdx.x; i < n_anc * ts; i += kThreads) {
+      for (int i = threadIdx.x; i < ((p.debug & 8) ? 0 : n_anc * ts); i += kThreads) {
         const int a = i / ts, s = i - a * ts;
         const float* S = sS + a * ldt + s * Q;
         const float* D = sD + a * ldt + s * Q;
@@ -270,7 +259,7 @@ __global__ void __launch_bounds__(kThreads) fit_ancestors_kernel(const FitParams
       __threadfence();
       atomicAdd(p.bar, 1ULL);
       const unsigned long long want = (unsigned long long)(it + 1) * G;
-      while (ld_acquire(p.bar) < want) {}
+      if (!(p.debug & 1)) while (ld_acquire(p.bar) < want) {}
     }
     __syncthreads();
     cost = norm2 = 0.0;
@@ -287,7 +276,7 @@ __global__ void __launch_bounds__(kThreads) fit_ancestors_kernel(const FitParams
     const float t = (float)(p.count0 + it + 1);
     const float b1 = 0.9f, b2 = 0.999f, eps = 1e-8f;
     const float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
-    for (int i = threadIdx.x; i < n_anc * ncols; i += kThreads) {
+    for (int i = threadIdx.x; i < ((p.debug & 4) ? 0 : n_anc * ncols); i += kThreads) {
       const int a = i / ncols, c = i - a * ncols;
       const size_t o = (size_t)a * ld + c;
       float g = gr[o];
@@ -337,8 +326,8 @@ __global__ void __launch_bounds__(kThreads) fit_ancestors_kernel(const FitParams
 }
 
 struct FitLayout {
-  size_t a2, bias, grad, slots, c0, bar, total;
-  int grid, sites_per_cta, tile_sites, resident;
+  size_t a2, bias, grad, ell_idx, ell_val, slots, c0, bar, ell_ok, tail, total;
+  int grid, sites_per_cta, tile_sites, resident, fast;
   size_t smem;
 };
 
@@ -349,21 +338,45 @@ FitLayout fit_layout(int N, int n_leaves, long long L, int Q) {
   int g = (int)std::min<long long>(L, sm_count());
   f.sites_per_cta = (int)((L + g - 1) / g);
   f.grid = (int)((L + f.sites_per_cta - 1) / f.sites_per_cta);
-  f.tile_sites = std::max(1, std::min(f.sites_per_cta, kTileCols / Q));
-  const int lda = (n_anc + 3) & ~3;
-  const int ldt = f.tile_sites * Q + 4 - ((f.tile_sites * Q) & 3);
-  const size_t base = sizeof(float) * ((size_t)n_anc * lda + 2 * (size_t)n_anc * ldt);
-  const size_t res = sizeof(float) * 5 * (size_t)n_anc * (((size_t)f.sites_per_cta * Q + 3) & ~(size_t)3);
-  f.resident = base + res <= 200 * 1024;
-  f.smem = base + (f.resident ? res : 0);
+  const size_t budget = 220 * 1024;
+  f.fast = (Q == 4 || Q == 20) && n_anc <= kMaxAnc;
+  if (const char* e = getenv("TREX_FIT_PATH")) {  // tests: "generic" forces the scalar kernel
+    if (e[0] == 'g') f.fast = 0;
+  }
+  if (f.fast) {
+    const size_t per_site = sizeof(float) * (size_t)n_anc * Q;
+    f.tile_sites = (int)std::max<size_t>(1, std::min<size_t>(f.sites_per_cta, (64 * 1024) / per_site));
+    // as many of the five state arrays as fit stay in shared memory (theta, grad, mom1, mom2, bias: bits 0..4);
+    // a smaller softmax tile is traded for one more resident array
+    f.resident = 0;
+    const int tile_min = std::min(f.sites_per_cta, (kFastThreads + n_anc - 1) / n_anc);  // a tile keeps every thread busy
+    int n_res = 0;
+    while (n_res < 5 && fit_fast_smem(n_anc, Q, f.sites_per_cta, tile_min, n_res + 1) <= budget) ++n_res;
+    f.resident = (1 << n_res) - 1;
+    f.tile_sites = std::max(f.tile_sites, tile_min);
+    while (f.tile_sites > tile_min && fit_fast_smem(n_anc, Q, f.sites_per_cta, f.tile_sites, n_res) > budget) --f.tile_sites;
+    f.smem = fit_fast_smem(n_anc, Q, f.sites_per_cta, f.tile_sites, n_res);
+  } else {
+    f.tile_sites = std::max(1, std::min(f.sites_per_cta, kTileCols / Q));
+    const int lda = (n_anc + 3) & ~3;
+    const int ldt = f.tile_sites * Q + 4 - ((f.tile_sites * Q) & 3);
+    const size_t base = sizeof(float) * ((size_t)n_anc * lda + 2 * (size_t)n_anc * ldt);
+    const size_t res = sizeof(float) * 5 * (size_t)n_anc * (((size_t)f.sites_per_cta * Q + 3) & ~(size_t)3);
+    f.resident = base + res <= budget ? 31 : 0;
+    f.smem = base + (f.resident ? res : 0);
+  }
   auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
   f.a2 = 0;
   f.bias = up(sizeof(float) * (size_t)N * N);
   f.grad = f.bias + up(sizeof(float) * (size_t)n_anc * K);
-  f.slots = f.grad + up(sizeof(float) * (size_t)n_anc * K);
-  f.c0 = f.slots + up(sizeof(double) * 4 * (size_t)f.grid);
+  f.ell_idx = f.grad + up(sizeof(float) * (size_t)n_anc * K);
+  f.ell_val = f.ell_idx + up(sizeof(int32_t) * (size_t)n_anc * kEll);
+  f.slots = f.ell_val + up(sizeof(float) * (size_t)n_anc * kEll);  // zeroed per call from here on
+  f.c0 = f.slots + up(sizeof(double) * 2 * kSlotDoubles * (size_t)f.grid);
   f.bar = f.c0 + 64;
-  f.total = f.bar + 64;
+  f.ell_ok = f.bar + 64;
+  f.tail = f.ell_ok + 64 - f.slots;
+  f.total = f.ell_ok + 64;
   return f;
 }
 
@@ -416,8 +429,21 @@ int trex_fit_ancestors(const float* adjacency, const float* leaf_seqs, int n_nod
   p.opt = optimizer; p.lr = learning_rate; p.clip = clip_norm; p.weight_decay = 0.01f;
   p.n_iter = n_iterations; p.count0 = step_count;
   p.sites_per_cta = f.sites_per_cta; p.tile_sites = f.tile_sites; p.resident = f.resident;
+  { const char* e = getenv("TREX_FIT_DEBUG"); p.debug = e ? atoi(e) : 0; }
 
-  int rc = check_cuda(cudaMemsetAsync(ws + f.c0, 0, 128, s), "cudaMemsetAsync(fit c0/barrier)");
+  p.ell_idx = (const int32_t*)(ws + f.ell_idx);
+  p.ell_val = (const float*)(ws + f.ell_val);
+  p.ell_ok = (const int32_t*)(ws + f.ell_ok);
+  const bool aligned = (((uintptr_t)ancestor_logits | (uintptr_t)opt_mom1 | (uintptr_t)opt_mom2 | (uintptr_t)workspace) & 15) == 0;
+  const bool fast = f.fast && aligned;
+  if (f.fast && !aligned) {
+    set_error("trex_fit_ancestors: ancestor_logits / opt_mom1 / opt_mom2 / workspace must be 16-byte aligned");
+    return TREX_ERR_INVALID_ARGUMENT;
+  }
+
+  int rc = check_cuda(cudaMemsetAsync(ws + f.slots, 0, f.tail, s), "cudaMemsetAsync(fit slots/c0/barrier)");
+  if (rc) return rc;
+  rc = check_cuda(cudaMemsetAsync(ws + f.ell_ok, 1, 1, s), "cudaMemsetAsync(fit ell_ok)");  // little-endian 1
   if (rc) return rc;
   fit_a2_kernel<<<n_nodes, 128, 0, s>>>(adjacency, n_nodes, (float*)(ws + f.a2));
   note_launches(1);
@@ -427,6 +453,13 @@ int trex_fit_ancestors(const float* adjacency, const float* leaf_seqs, int n_nod
   note_launches(1);
   TREX_CHECK_LAUNCH("fit_bias_kernel");
 
+  if (fast) {
+    fit_ell_kernel<<<(n_anc + 127) / 128, 128, 0, s>>>(p.a2, n_nodes, n_leaves, (int32_t*)(ws + f.ell_idx),
+                                                      (float*)(ws + f.ell_val), (int32_t*)(ws + f.ell_ok));
+    note_launches(1);
+    TREX_CHECK_LAUNCH("fit_ell_kernel");
+    return launch_fit_fast(p, f.grid, f.smem, s);
+  }
   rc = check_cuda(cudaFuncSetAttribute(fit_ancestors_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)f.smem),
                   "cudaFuncSetAttribute(fit_ancestors_kernel)");
   if (rc) return rc;
