@@ -413,26 +413,55 @@ def run_gpu(args):
              for i, nm in enumerate(names)}
 
   # ---- end-to-end: host buffers in, host results out, through the public API ------------------
-  def e2e_step():
-    adj_x = adj_p.cuda(non_blocking=True)
-    cost_x = cost_p.cuda(non_blocking=True)
-    states_x = states_p.cuda(non_blocking=True)
-    eng.set_leaf_states_u8(states_x)
-    eng.set_adjacency(adj_x)
-    eng.hard_forward(cost_x, want_argmin=True)
-    eng.traceback(want_hist=True)
-    eng.soft_forward(cost_x, SOFT_T)
-    eng.soft_backward(cost_x, SOFT_T, want_dleaf=True, want_dcost=True)
-    reducer([eng.total, eng.soft_total, eng.dcost, eng.edge_hist])
-    packed_h.copy_(reducer.buf, non_blocking=True)
+  # Successive steps are independent alignments, so the pinned-host -> device copies of step k+1 (leaf
+  # states, adjacency, cost matrix) run on a copy stream under the kernels of step k: two leaf tables and
+  # two adjacency / cost buffers alternate; every other table is shared.  All K copies happen inside the
+  # timed region (the first one is not overlapped with anything).
+  engs = [eng, eng.site_block(0, L)]
+  engs[1]._bufs["leaf"] = torch.empty_like(eng.leaf)
+  engs[1]._pad_owner = True
+  adj_x = [torch.empty_like(adj_d) for _ in range(2)]
+  cost_x = [torch.empty_like(cost_d) for _ in range(2)]
+  copy_stream = torch.cuda.Stream()
 
-  for _ in range(2):
-    e2e_step()
+  def upload(k):
+    j = k & 1
+    adj_x[j].copy_(adj_p, non_blocking=True)
+    cost_x[j].copy_(cost_p, non_blocking=True)
+    engs[j].set_leaf_states_u8(states_p)
+
+  def e2e_run(n_steps):
+    main = torch.cuda.current_stream()
+    ready = [torch.cuda.Event() for _ in range(n_steps)]
+    done = [torch.cuda.Event() for _ in range(n_steps)]
+    copy_stream.wait_stream(main)
+    with torch.cuda.stream(copy_stream):
+      upload(0)
+      ready[0].record(copy_stream)
+    for k in range(n_steps):
+      j = k & 1
+      e = engs[j]
+      main.wait_event(ready[k])
+      if k + 1 < n_steps:
+        with torch.cuda.stream(copy_stream):
+          if k >= 1:
+            copy_stream.wait_event(done[k - 1])  # step k-1 used the buffers step k+1 uploads into
+          upload(k + 1)
+          ready[k + 1].record(copy_stream)
+      e.set_adjacency(adj_x[j])
+      e.hard_forward(cost_x[j], want_argmin=True)
+      e.traceback(want_hist=True)
+      e.soft_forward(cost_x[j], SOFT_T)
+      e.soft_backward(cost_x[j], SOFT_T, want_dleaf=True, want_dcost=True)
+      done[k].record(main)
+      reducer([e.total, e.soft_total, e.dcost, e.edge_hist])
+      packed_h.copy_(reducer.buf, non_blocking=True)
+
+  e2e_run(2)
   barrier()
   f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
   f0.record()
-  for _ in range(args.steps):
-    e2e_step()
+  e2e_run(args.steps)
   f1.record()
   barrier()
   ms_e2e = f0.elapsed_time(f1)
@@ -469,7 +498,9 @@ def run_gpu(args):
       "kernel_ms": kern_ms,
       "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
               "h2d_bytes_per_step": int(states_p.numel() + adj_p.numel() * 4 + cost_p.numel() * 4),
-              "d2h_bytes_per_step": int(packed_h.numel() * 8)},
+              "d2h_bytes_per_step": int(packed_h.numel() * 8),
+              "overlap": "H2D of step k+1 on a copy stream under the kernels of step k (double-buffered inputs)",
+              "results": {"hard_total": float(packed_h[0]), "soft_total": float(packed_h[1])}},
       "gpu_launches": gpu_launches,
       "clocks": clocks,
       "results": {"hard_total": float(packed_h[0]), "soft_total": float(packed_h[1])},

@@ -309,3 +309,49 @@ def test_internal_node_the_root_does_not_reach(ck):
   eng.traceback()
   want = so.traceback_topdown(tabs, n_all, n)
   assert np.array_equal(eng.anc[0, :, :L].cpu().numpy(), want[n:].astype(np.uint8))
+
+
+def test_site_blocks_add_up_to_the_whole_alignment():
+  """Streaming an alignment in site blocks (SankoffEngine.site_block: views of the same tables) gives the
+  same tables, and per-block totals / dC / edge histograms that add up to the single-call results."""
+  import torch
+  from trex_b200 import synth
+  from trex_b200.sankoff import SankoffEngine
+
+  rng = np.random.default_rng(11)
+  n, A, L = 32, 20, 1000
+  parent = synth.balanced_parents(n)
+  states = synth.evolve(parent, L, A, 0.15, rng)[:n]
+  adj = torch.from_numpy(synth.parents_to_adjacency(parent).astype(np.float32)).cuda()
+  cost = torch.from_numpy(synth.unit_cost(A)).cuda()
+  st = torch.from_numpy(states).cuda()
+
+  def run(e):
+    e.hard_forward(cost, want_argmin=True)
+    e.traceback(want_hist=True)
+    e.soft_forward(cost, 0.7)
+    e.soft_backward(cost, 0.7, want_dleaf=True, want_dcost=True)
+
+  whole = SankoffEngine(2 * n - 1, n, A, L)
+  whole.set_adjacency(adj)
+  whole.set_leaf_states_u8(st)
+  run(whole)
+  ref = {k: getattr(whole, k).clone() for k in ("dp", "anc", "soft_dp", "gbar", "dleaf", "total", "soft_total", "dcost", "edge_hist")}
+
+  eng = SankoffEngine(2 * n - 1, n, A, L)
+  eng.set_adjacency(adj)
+  blocks = eng.site_blocks(3)
+  assert sum(b.L for b in blocks) == L and len(blocks) == 3
+  tot = {k: torch.zeros_like(ref[k]) for k in ("total", "soft_total", "dcost", "edge_hist")}
+  lo = 0
+  for b in blocks:
+    b.set_leaf_states_u8(st[:, lo:lo + b.L])
+    lo += b.L
+    run(b)
+    for k in tot:
+      tot[k] += getattr(b, k)
+  for k in ("dp", "anc", "soft_dp", "gbar", "dleaf"):
+    assert torch.equal(getattr(eng, k)[..., :L], ref[k][..., :L]), k
+  assert torch.equal(tot["total"], ref["total"]) and torch.equal(tot["edge_hist"], ref["edge_hist"])
+  assert abs(float(tot["soft_total"]) - float(ref["soft_total"])) <= 1e-9 * abs(float(ref["soft_total"]))
+  assert torch.allclose(tot["dcost"], ref["dcost"], rtol=1e-9, atol=0)

@@ -104,6 +104,30 @@ class SankoffEngine:
   def edge_hist(self):
     return self.buf("edge_hist", (self.batch, self.A, self.A), torch.int64)
 
+  # -- site blocks ----------------------------------------------------------------------------
+  _SITE_TABLES = ("leaf", "dp", "argmin", "anc", "root_min", "soft_dp", "gbar", "dleaf")
+
+  def site_block(self, lo: int, hi: int):
+    """An engine over sites [lo, hi) of this one's tables (views, no copies; ``lo`` a multiple of 64).
+
+    Sites are independent under Sankoff (sankoff.py:97), so a long alignment can be streamed in
+    blocks: the host->device copy of block b+1 overlaps the kernels of block b (``bench.py`` e2e leg).
+    The plan is shared; totals / dC / edge histogram are per block and add up over the blocks."""
+    lo, hi = int(lo), int(hi)
+    assert 0 <= lo < hi <= self.L and lo % 64 == 0, (lo, hi)
+    blk = SankoffEngine.__new__(SankoffEngine)
+    blk.__dict__.update({k: v for k, v in self.__dict__.items() if k != "_bufs"})
+    blk.L = hi - lo
+    blk._pad_owner = hi == self.L  # only the last block may touch the pad columns of the row pitch
+    blk._bufs = {"plan": self.plan}
+    for name in self._SITE_TABLES:
+      blk._bufs[name] = getattr(self, name)[..., lo:]
+    return blk
+
+  def site_blocks(self, n_blocks: int):
+    per = max(64, ((self.L + n_blocks - 1) // n_blocks + 63) // 64 * 64)
+    return [self.site_block(lo, min(self.L, lo + per)) for lo in range(0, self.L, per)]
+
   # -- inputs -------------------------------------------------------------------------------
   def set_adjacency(self, adj, zero_root_selfloop=True):
     """adj: (n_all, n_all) or (batch, n_all, n_all), any numeric dtype (cast to f32 as
@@ -118,8 +142,8 @@ class SankoffEngine:
 
   def set_leaf_states_u8(self, states):
     """states: (n_leaves, L) uint8 codes (>= A means 'no state')."""
-    self.leaf[:, : self.L].copy_(states.to(self.device)[: self.n_leaves], non_blocking=True)
-    if self.stride > self.L:
+    self.leaf[:, : self.L].copy_(states[: self.n_leaves], non_blocking=True)
+    if getattr(self, "_pad_owner", True) and self.leaf.shape[1] > self.L:
       self.leaf[:, self.L:].fill_(255)
     return self
 
