@@ -45,6 +45,31 @@ __device__ __forceinline__ void axpy_row(float w, const float* __restrict__ row,
   for (int q = 0; q < Q; ++q) acc[q] = fmaf(w, r[q], acc[q]);
 }
 
+// One row of the optimiser update (evals/benchmark.py:41-72); g is the raw gradient, gscale the clip factor.
+// mu: first moment (adam, adamw) or momentum trace (sgd); nu: second moment (adam, adamw, rmsprop).
+template <int Q>
+__device__ __forceinline__ void opt_row(int opt, float lr, float wd, float ibc1, float ibc2, float gscale,
+                                        const float (&g0)[Q], float (&x)[Q], float (&mu)[Q], float (&nu)[Q]) {
+  const float b1 = 0.9f, b2 = 0.999f, eps = 1e-8f;
+#pragma unroll
+  for (int q = 0; q < Q; ++q) {
+    const float g = g0[q] * gscale;
+    if (opt == OPT_SGD) {  // optax.sgd(lr, momentum=0.9): trace
+      mu[q] = fmaf(0.9f, mu[q], g);
+      x[q] = fmaf(-lr, mu[q], x[q]);
+    } else if (opt == OPT_RMSPROP) {  // optax.rmsprop(lr): decay 0.9, eps 1e-8 inside the sqrt
+      nu[q] = fmaf(0.9f, nu[q], (1.f - 0.9f) * g * g);
+      x[q] = fmaf(-lr, g * rsqrtf(nu[q] + eps), x[q]);
+    } else {  // optax.adam / adamw(weight_decay=0.01)
+      mu[q] = fmaf(b1, mu[q], (1.f - b1) * g);
+      nu[q] = fmaf(b2, nu[q], (1.f - b2) * (g * g));
+      float u = __fdividef(mu[q] * ibc1, sqrtf(nu[q] * ibc2) + eps);
+      if (opt == OPT_ADAMW) u = fmaf(wd, x[q], u);
+      x[q] = fmaf(-lr, u, x[q]);
+    }
+  }
+}
+
 template <int Q>
 __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
   extern __shared__ __align__(16) float smem[];
@@ -106,7 +131,7 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
   }
   __syncthreads();
   const double c0 = *p.c0;
-  const float b1 = 0.9f, b2 = 0.999f, eps = 1e-8f;
+  const float b1 = 0.9f, b2 = 0.999f;
   double pw1 = pow((double)b1, (double)p.count0), pw2 = pow((double)b2, (double)p.count0);  // b^t, kept running
 
   long long prof[6] = {0, 0, 0, 0, 0, 0}, tk = clock64();
@@ -188,6 +213,37 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
     if (lane == 0) { red[warp] = (double)fc; red[NW + warp] = (double)fn; }
     __syncthreads();
     tick(1);
+    pw1 *= (double)b1;
+    pw2 *= (double)b2;
+    const float ibc1 = 1.f / (1.f - (float)pw1), ibc2 = 1.f / (1.f - (float)pw2);
+    const int nupd = (p.debug & 4) ? 0 : n_anc * nsites;
+    // Row state of the update in registers.  When a CTA has at most one row per thread (c2), the warps that
+    // do not poll run the update while the barrier is in flight, assuming the gradient is not clipped
+    // (|g| < clip: the common case away from the first iterations); a clipped step is simply redone.
+    float ug[Q], ux[Q], umu[Q], unu[Q];
+    size_t og, ox, o1, o2;
+    auto load_rows = [&](int i) {
+      const int a = i / nsites, s = i - a * nsites;
+      og = (size_t)a * ld_gr + s * Q; ox = (size_t)a * ld_th + s * Q;
+      o1 = (size_t)a * ld_m1 + s * Q; o2 = (size_t)a * ld_m2 + s * Q;
+      ld_row<Q>(gr + og, ug);
+      ld_row<Q>(th + ox, ux);
+      if (p.opt != OPT_RMSPROP) ld_row<Q>(m1 + o1, umu);
+      if (p.opt != OPT_SGD) ld_row<Q>(m2 + o2, unu);
+    };
+    auto store_rows = [&](int) {
+      if (p.opt != OPT_RMSPROP) st_row<Q>(m1 + o1, umu);
+      if (p.opt != OPT_SGD) st_row<Q>(m2 + o2, unu);
+      st_row<Q>(th + ox, ux);
+    };
+    // (warp 0 polls, so it owns no row: row r belongs to thread r + 32)
+    const bool spec = Q <= 4 && n_anc * nsites <= NT - 32;
+    bool spec_done = false;
+    if (spec && warp != 0 && tid - 32 < nupd) {
+      load_rows(tid - 32);
+      opt_row<Q>(p.opt, p.lr, p.weight_decay, ibc1, ibc2, 1.f, ug, ux, umu, unu);
+      spec_done = true;
+    }
     if (warp == 0) {
       const unsigned long long tag = (unsigned long long)((it + 1) & 3);
       unsigned long long* slots = reinterpret_cast<unsigned long long*>(p.slots) + (size_t)(it & 1) * kSlotDoubles * G;
@@ -238,50 +294,21 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
     // ---- B: optax.clip_by_global_norm + the optimiser (evals/benchmark.py:41-72) -------------------
     const float gnorm = sqrtf((float)norm2);
     const float gscale = (p.clip > 0.f && !(gnorm < p.clip)) ? p.clip / gnorm : 1.f;
-    pw1 *= (double)b1;
-    pw2 *= (double)b2;
-    const float ibc1 = 1.f / (1.f - (float)pw1), ibc2 = 1.f / (1.f - (float)pw2);
-    const int nupd = (p.debug & 4) ? 0 : n_anc * nsites;
-    for (int i = tid; i < nupd; i += NT) {
-      const int a = i / nsites, s = i - a * nsites;
-      const size_t og = (size_t)a * ld_gr + s * Q, ox = (size_t)a * ld_th + s * Q;
-      const size_t o1 = (size_t)a * ld_m1 + s * Q, o2 = (size_t)a * ld_m2 + s * Q;
-      float g[Q], x[Q];
-      ld_row<Q>(gr + og, g);
-      ld_row<Q>(th + ox, x);
-#pragma unroll
-      for (int q = 0; q < Q; ++q) g[q] *= gscale;
-      if (p.opt == OPT_SGD) {  // optax.sgd(lr, momentum=0.9): trace
-        float tr[Q];
-        ld_row<Q>(m1 + o1, tr);
-#pragma unroll
-        for (int q = 0; q < Q; ++q) { tr[q] = fmaf(0.9f, tr[q], g[q]); x[q] = fmaf(-p.lr, tr[q], x[q]); }
-        st_row<Q>(m1 + o1, tr);
-      } else if (p.opt == OPT_RMSPROP) {  // optax.rmsprop(lr): decay 0.9, eps 1e-8 inside the sqrt
-        float nu[Q];
-        ld_row<Q>(m2 + o2, nu);
-#pragma unroll
-        for (int q = 0; q < Q; ++q) {
-          nu[q] = fmaf(0.9f, nu[q], (1.f - 0.9f) * g[q] * g[q]);
-          x[q] = fmaf(-p.lr, g[q] * rsqrtf(nu[q] + eps), x[q]);
+    if (spec) {
+      // the rows were updated ahead of the barrier on the assumption that nothing is clipped (see above)
+      if (spec_done) {
+        if (gscale != 1.f) {
+          load_rows(tid - 32);
+          opt_row<Q>(p.opt, p.lr, p.weight_decay, ibc1, ibc2, gscale, ug, ux, umu, unu);
         }
-        st_row<Q>(m2 + o2, nu);
-      } else {  // optax.adam / adamw(weight_decay=0.01)
-        float mu[Q], nu[Q];
-        ld_row<Q>(m1 + o1, mu);
-        ld_row<Q>(m2 + o2, nu);
-#pragma unroll
-        for (int q = 0; q < Q; ++q) {
-          mu[q] = fmaf(b1, mu[q], (1.f - b1) * g[q]);
-          nu[q] = fmaf(b2, nu[q], (1.f - b2) * (g[q] * g[q]));
-          float u = __fdividef(mu[q] * ibc1, sqrtf(nu[q] * ibc2) + eps);
-          if (p.opt == OPT_ADAMW) u = fmaf(p.weight_decay, x[q], u);
-          x[q] = fmaf(-p.lr, u, x[q]);
-        }
-        st_row<Q>(m1 + o1, mu);
-        st_row<Q>(m2 + o2, nu);
+        store_rows(tid - 32);
       }
-      st_row<Q>(th + ox, x);
+    } else {
+      for (int i = tid; i < nupd; i += NT) {
+        load_rows(i);
+        opt_row<Q>(p.opt, p.lr, p.weight_decay, ibc1, ibc2, gscale, ug, ux, umu, unu);
+        store_rows(i);
+      }
     }
     __syncthreads();
     tick(5);

@@ -116,6 +116,31 @@ ffi::Error TreeCostImpl(cudaStream_t stream, ffi::ScratchAllocator scratch, ffi:
   return ffi::Error::Success();
 }
 
+// run_trex_optimization_configurable (src/trex/evals/benchmark.py:75-200): the whole fori_loop / scan.
+// `logits` is aliased to result 0 by the Python wrapper (input_output_aliases), the moments start at zero.
+ffi::Error FitAncestorsImpl(cudaStream_t stream, ffi::ScratchAllocator scratch, ffi::Buffer<ffi::F32> adj,
+                            ffi::Buffer<ffi::F32> leaf_seqs, ffi::Buffer<ffi::F32> logits, int32_t optimizer,
+                            float learning_rate, float clip_norm, int32_t n_iterations,
+                            ffi::ResultBuffer<ffi::F32> out_logits, ffi::ResultBuffer<ffi::F32> mom1,
+                            ffi::ResultBuffer<ffi::F32> mom2, ffi::ResultBuffer<ffi::F32> losses,
+                            ffi::ResultBuffer<ffi::S32> argmax) {
+  const int N = (int)adj.dimensions()[0];
+  const int n_leaves = (int)leaf_seqs.dimensions()[0];
+  const int64_t L = leaf_seqs.dimensions()[1];
+  const int Q = (int)leaf_seqs.dimensions()[2];
+  const size_t bytes = sizeof(float) * (size_t)(N - n_leaves) * L * Q;
+  if (out_logits->typed_data() != logits.typed_data())
+    cudaMemcpyAsync(out_logits->typed_data(), logits.typed_data(), bytes, cudaMemcpyDeviceToDevice, stream);
+  cudaMemsetAsync(mom1->typed_data(), 0, bytes, stream);
+  cudaMemsetAsync(mom2->typed_data(), 0, bytes, stream);
+  auto ws = scratch.Allocate(trex_fit_ancestors_workspace_bytes(N, n_leaves, L, Q));
+  if (!ws.has_value()) return ffi::Error::Internal("trex fit_ancestors: scratch allocation failed");
+  TREX_TRY(trex_fit_ancestors(adj.typed_data(), leaf_seqs.typed_data(), N, n_leaves, L, Q, out_logits->typed_data(),
+                              mom1->typed_data(), mom2->typed_data(), optimizer, learning_rate, clip_norm,
+                              n_iterations, 0, losses->typed_data(), argmax->typed_data(), *ws, stream));
+  return ffi::Error::Success();
+}
+
 }  // namespace
 
 XLA_FFI_DEFINE_HANDLER_SYMBOL(trex_run_sankoff_ffi, RunSankoffImpl,
@@ -173,3 +198,20 @@ XLA_FFI_DEFINE_HANDLER_SYMBOL(trex_tree_cost_ffi, TreeCostImpl,
                                   .Ret<ffi::Buffer<ffi::F32>>()
                                   .Ret<ffi::Buffer<ffi::F32>>()
                                   .Ret<ffi::Buffer<ffi::F32>>());
+
+XLA_FFI_DEFINE_HANDLER_SYMBOL(trex_fit_ancestors_ffi, FitAncestorsImpl,
+                              ffi::Ffi::Bind()
+                                  .Ctx<ffi::PlatformStream<cudaStream_t>>()
+                                  .Ctx<ffi::ScratchAllocator>()
+                                  .Arg<ffi::Buffer<ffi::F32>>()
+                                  .Arg<ffi::Buffer<ffi::F32>>()
+                                  .Arg<ffi::Buffer<ffi::F32>>()
+                                  .Attr<int32_t>("optimizer")
+                                  .Attr<float>("learning_rate")
+                                  .Attr<float>("clip_norm")
+                                  .Attr<int32_t>("n_iterations")
+                                  .Ret<ffi::Buffer<ffi::F32>>()
+                                  .Ret<ffi::Buffer<ffi::F32>>()
+                                  .Ret<ffi::Buffer<ffi::F32>>()
+                                  .Ret<ffi::Buffer<ffi::F32>>()
+                                  .Ret<ffi::Buffer<ffi::S32>>());
