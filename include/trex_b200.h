@@ -209,6 +209,22 @@ TREX_API int trex_fit_ancestors(const float* adjacency, const float* leaf_seqs, 
                        int optimizer, float learning_rate, float clip_norm, int n_iterations, int64_t step_count,
                        float* out_losses, int32_t* out_argmax, void* workspace, void* stream);
 
+/* ---- landscape-aware ("parental guidance") loss term --------------------------
+ * compute_parental_logits (src/trex/evals/benchmark.py:586-663) and the fitness_cost part of
+ * _compute_loss_landscape_aware_stacked (:283-303):  parent p = argmax_j Adj[n][j];
+ * logits[n][i][s] = sum_j F_i[s * Q^k + j] * prod_m S[p][interactions[i][m]][digit_m(j)];
+ * fitness_cost = -sum_{n,i} mask[i] sum_s S[n][i][s] log_softmax(logits[n][i])[s] / (#non-root nodes * sum(mask)).
+ *   seqs [N][L][Q] f32 (the updated sequences); adjacency [N][N] f32 or NULL when parent_index [N] i32 is given
+ *   (compute_parental_logits itself takes the parents' rows: pass them as seqs with parent_index = 0..N-1)
+ *   interactions [L][k] i32; fitness_tables [L][Q^(k+1)] f32; seq_mask [L] f32 (0/1) or NULL; 0 <= k <= 3, Q <= 32
+ *   out_fitness_cost f32 scalar or NULL; out_logits [N][L][Q] or NULL; d_seqs [N][L][Q] or NULL
+ *   (d fitness_cost / d seqs, both the child and the parent path); parent_scratch [N] i32; acc_scratch 2 f64. */
+TREX_API int trex_landscape_loss_fwd_bwd(const float* seqs, const float* adjacency, const int32_t* parent_index,
+                                const int32_t* interactions, const float* fitness_tables, const float* seq_mask,
+                                int n_nodes, int64_t n_sites, int n_states, int k, float* out_fitness_cost,
+                                float* out_logits, float* d_seqs, int32_t* parent_scratch, double* acc_scratch,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif

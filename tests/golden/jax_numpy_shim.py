@@ -172,7 +172,8 @@ def install():
   jax._IS_NUMPY_SHIM = True
   jnp = types.ModuleType("jax.numpy")
   for name in ["zeros", "ones", "full", "arange", "eye", "stack", "concatenate", "zeros_like", "ones_like",
-               "array", "asarray", "isnan", "isclose", "allclose", "log", "exp"]:
+               "array", "asarray", "isnan", "isclose", "allclose", "log", "exp", "einsum", "broadcast_to",
+               "transpose", "sqrt", "abs", "mean"]:
     def mk(fn):
       return lambda *a, **k: _wrap(fn(*a, **k))
     setattr(jnp, name, mk(getattr(np, name)))
@@ -187,10 +188,14 @@ def install():
   jnp.inf, jnp.newaxis, jnp.ndarray = np.inf, np.newaxis, np.ndarray
   jnp.int32, jnp.int8, jnp.float32, jnp.float64, jnp.bfloat16 = np.int32, np.int8, np.float32, np.float64, np.float32
   jnp.dtype = np.dtype
+  jnp.bool_ = np.bool_
   lax = types.ModuleType("jax.lax")
   lax.fori_loop, lax.scan, lax.while_loop, lax.cond = _fori_loop, _scan, _while_loop, _cond
   nn = types.ModuleType("jax.nn")
   nn.softmax, nn.one_hot = _softmax, _one_hot
+  nn.log_softmax = lambda x, axis=-1: _wrap(np.log(np.asarray(_softmax(x, axis=axis))))
+  # lax.map(f, xs, batch_size=...) == stack of f(x) over the leading axis (utils/memory.py:28)
+  lax.map = lambda f, xs, batch_size=None: _wrap(np.stack([np.asarray(f(x)) for x in np.asarray(xs)]))
   random = types.ModuleType("jax.random")
   random.PRNGKey = random.key = lambda seed: _wrap(np.array([0, seed], dtype=np.uint32))
   random.split = lambda key, num=2: _wrap(np.stack([np.asarray(key)] * num))
@@ -202,6 +207,25 @@ def install():
   jax.numpy, jax.lax, jax.nn, jax.random, jax.debug, jax.tree_util = jnp, lax, nn, random, debug, tree_util
   jax.jit, jax.vmap, jax.Array = _jit, _vmap, np.ndarray
   jax.block_until_ready = lambda x: x
+
+  class _CustomVjp:  # jax.custom_vjp: the primal function, defvjp ignored (no autodiff in the stand-in)
+    def __init__(self, fn, **_):
+      self.fn = fn
+
+    def __call__(self, *a, **k):
+      return self.fn(*a, **k)
+
+    def defvjp(self, *a, **k):
+      return None
+
+  jax.custom_vjp = _CustomVjp
+
+  def _no_autodiff(fn, *a, **k):  # may be built at import time (evals/benchmark.py:807), must not be called
+    def call(*aa, **kk):
+      raise NotImplementedError("no autodiff in the NumPy stand-in")
+    return call
+
+  jax.value_and_grad = jax.grad = _no_autodiff
   for name, mod in [("jax", jax), ("jax.numpy", jnp), ("jax.lax", lax), ("jax.nn", nn), ("jax.random", random),
                     ("jax.debug", debug), ("jax.tree_util", tree_util)]:
     sys.modules[name] = mod
