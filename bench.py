@@ -328,6 +328,46 @@ def fit_loop_bench(torch):
                            "sample": "3 iterations of the NumPy float32 restatement of the loop at c2 (optax/JAX absent)"}}
 
 
+def landscape_bench(torch, iters=50):
+  """the parental-guidance term of _compute_loss_landscape_aware_stacked
+  (evals/benchmark.py:283-303) — value + d/dS in one library call, NK landscape with K = 1, q = 20
+  (evals/benchmark.py:922-929) at 255 nodes x 1000 sites; CPU: the NumPy float64 restatement, one call."""
+  from oracle import landscape_oracle as lo
+  from oracle import tree_oracle as to
+  from trex_b200 import landscape as LS
+  from trex_b200 import synth
+
+  n, L, Q, k = 128, 1000, 20, 1
+  rng = np.random.default_rng(7)
+  parent = synth.balanced_parents(n)
+  N = parent.shape[0]
+  adj = synth.parents_to_adjacency(parent).astype(np.float32)
+  S = to.softmax(rng.normal(size=(N, L, Q))).astype(np.float32)
+  inter = rng.integers(0, L, size=(L, k)).astype(np.int32)
+  tables = rng.random((L, Q ** (k + 1))).astype(np.float32)
+  land = {"interactions": torch.from_numpy(inter).cuda(), "fitness_tables": torch.from_numpy(tables).cuda()}
+  St, At = torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda()
+  it_, tb, kk = LS._landscape_arrays(land, k, St.device)
+  call = lambda: LS._call(St, At, None, it_, tb, None, kk, True, False, True)
+  for _ in range(5):
+    call()
+  e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+  torch.cuda.synchronize()
+  e0.record()
+  for _ in range(iters):
+    cost, _, dS = call()
+  e1.record()
+  torch.cuda.synchronize()
+  ms = e0.elapsed_time(e1) / iters
+  t0 = time.perf_counter()
+  ref = lo.fitness_cost(S, adj, inter, tables, k)
+  lo.fitness_cost_grad(S, adj, inter, tables, k)
+  cpu_ms = (time.perf_counter() - t0) * 1e3
+  return {"shape": f"{N} nodes x {L} sites x {Q} states, K = {k}", "ms_per_value_and_grad": ms,
+          "value_and_grads_per_s": 1e3 / ms, "cpu_ms_per_value_and_grad": cpu_ms,
+          "rel_err_vs_float64_port": abs(float(cost) - ref) / abs(ref)}
+
+
 def run_gpu(args):
   import torch
   import torch.distributed as dist
@@ -508,6 +548,7 @@ def run_gpu(args):
     if world == 1 and not args.no_extras:
       line["tree_cost"] = tree_cost_bench(torch)
       line["fit_loop"] = fit_loop_bench(torch)
+      line["landscape_loss"] = landscape_bench(torch)
       line["cpu_baseline"] = cpu_baseline(args.cpu_sites)
     emit(line)
   if world > 1:

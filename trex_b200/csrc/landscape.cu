@@ -55,13 +55,16 @@ __global__ void landscape_setup_kernel(const float* __restrict__ adj, const int3
   }
 }
 
-template <int K>
+// QT: compile-time alphabet (4, 20: every per-state array lives in registers) or 0 = run-time Q <= kMaxQ
+template <int K, int QT>
 __global__ void __launch_bounds__(kLsThreads)
     landscape_kernel(const float* __restrict__ S, const int32_t* __restrict__ parent, const int32_t* __restrict__ inter,
-                     const float* __restrict__ tables, const float* __restrict__ mask, int N, long long L, int Q,
+                     const float* __restrict__ tables, const float* __restrict__ mask, int N, long long L, int q_rt,
                      int table_in_smem, float* __restrict__ out_logits, float* __restrict__ dS,
                      double* __restrict__ scal) {
   extern __shared__ __align__(16) float sF[];
+  constexpr int QA = QT ? QT : kMaxQ;
+  const int Q = QT ? QT : q_rt;
   const long long site = blockIdx.x;
   int QK = 1;
 #pragma unroll
@@ -82,7 +85,7 @@ __global__ void __launch_bounds__(kLsThreads)
 
   for (int node = threadIdx.x; node < N; node += kLsThreads) {
     const int p = parent[node];
-    float P[K > 0 ? K : 1][kMaxQ], dP[K > 0 ? K : 1][kMaxQ];
+    float P[K > 0 ? K : 1][QA], dP[K > 0 ? K : 1][QA];
 #pragma unroll
     for (int m = 0; m < K; ++m)
       for (int t = 0; t < Q; ++t) {
@@ -90,9 +93,13 @@ __global__ void __launch_bounds__(kLsThreads)
         dP[m][t] = 0.f;
       }
     // logits[s] = sum_j F[s][j] joint[j]
-    float logit[kMaxQ];
-    for (int s = 0; s < Q; ++s) logit[s] = 0.f;
-    {
+    float logit[QA];
+    _Pragma("unroll") for (int s = 0; s < Q; ++s) logit[s] = 0.f;
+    if constexpr (K == 1 && QT > 0) {  // the benchmark's K: a Q x Q mat-vec, everything in registers
+#pragma unroll
+      for (int j = 0; j < QT; ++j)
+        _Pragma("unroll") for (int s = 0; s < Q; ++s) logit[s] = fmaf(F[s * QT + j], P[0][j], logit[s]);
+    } else {
       int d[K > 0 ? K : 1];
 #pragma unroll
       for (int m = 0; m < K; ++m) d[m] = 0;
@@ -100,7 +107,7 @@ __global__ void __launch_bounds__(kLsThreads)
         float joint = 1.f;
 #pragma unroll
         for (int m = 0; m < K; ++m) joint *= P[m][d[m]];
-        for (int s = 0; s < Q; ++s) logit[s] = fmaf(F[(size_t)s * QK + j], joint, logit[s]);
+        _Pragma("unroll") for (int s = 0; s < Q; ++s) logit[s] = fmaf(F[(size_t)s * QK + j], joint, logit[s]);
 #pragma unroll
         for (int m = K - 1; m >= 0; --m) {  // next digit vector, last neighbour fastest
           if (++d[m] < Q) break;
@@ -109,16 +116,16 @@ __global__ void __launch_bounds__(kLsThreads)
       }
     }
     if (out_logits)
-      for (int s = 0; s < Q; ++s) out_logits[((size_t)node * L + site) * Q + s] = logit[s];
+      _Pragma("unroll") for (int s = 0; s < Q; ++s) out_logits[((size_t)node * L + site) * Q + s] = logit[s];
     // masked cross-entropy of the child's distribution against log_softmax(logits)
     float mx = logit[0];
-    for (int s = 1; s < Q; ++s) mx = fmaxf(mx, logit[s]);
+    _Pragma("unroll") for (int s = 1; s < Q; ++s) mx = fmaxf(mx, logit[s]);
     float z = 0.f;
-    for (int s = 0; s < Q; ++s) z += expf(logit[s] - mx);
+    _Pragma("unroll") for (int s = 0; s < Q; ++s) z += expf(logit[s] - mx);
     const float lz = mx + logf(z);
     const float* child = S + ((size_t)node * L + site) * Q;
     float csum = 0.f, ce = 0.f;
-    for (int s = 0; s < Q; ++s) {
+    _Pragma("unroll") for (int s = 0; s < Q; ++s) {
       const float c = child[s];
       csum += c;
       ce -= c * (logit[s] - lz);
@@ -128,19 +135,26 @@ __global__ void __launch_bounds__(kLsThreads)
       const float w = w_site * wn;
       float* dchild = dS + ((size_t)node * L + site) * Q;
       // child path: -w log p;  parent path: d logits = w (softmax * sum(child) - child)
-      float dl[kMaxQ];
-      for (int s = 0; s < Q; ++s) {
+      float dl[QA];
+      _Pragma("unroll") for (int s = 0; s < Q; ++s) {
         const float lp = logit[s] - lz;
         atomicAdd(dchild + s, -w * lp);
         dl[s] = w * (expf(lp) * csum - child[s]);
       }
-      if (K > 0) {
+      if constexpr (K == 1 && QT > 0) {
+#pragma unroll
+        for (int j = 0; j < QT; ++j) {
+          float dj = 0.f;
+          _Pragma("unroll") for (int s = 0; s < Q; ++s) dj = fmaf(dl[s], F[s * QT + j], dj);
+          if (dj != 0.f) atomicAdd(dS + ((size_t)p * L + nb[0]) * Q + j, dj);
+        }
+      } else if (K > 0) {
         int d[K > 0 ? K : 1];
 #pragma unroll
         for (int m = 0; m < K; ++m) d[m] = 0;
         for (int j = 0; j < QK; ++j) {
           float dj = 0.f;
-          for (int s = 0; s < Q; ++s) dj = fmaf(dl[s], F[(size_t)s * QK + j], dj);
+          _Pragma("unroll") for (int s = 0; s < Q; ++s) dj = fmaf(dl[s], F[(size_t)s * QK + j], dj);
 #pragma unroll
           for (int m = 0; m < K; ++m) {
             float others = dj;
@@ -217,12 +231,21 @@ int trex_landscape_loss_fwd_bwd(const float* seqs, const float* adjacency, const
     return check_cuda(cudaPeekAtLastError(), "landscape_kernel");
   };
   int rc;
+#define TREX_LS_CASE(KK)                                                   \
+  case KK:                                                                 \
+    rc = n_states == 4    ? go(landscape_kernel<KK, 4>)                    \
+         : n_states == 20 ? go(landscape_kernel<KK, 20>)                   \
+                          : go(landscape_kernel<KK, 0>);                   \
+    break;
   switch (k) {
-    case 0: rc = go(landscape_kernel<0>); break;
-    case 1: rc = go(landscape_kernel<1>); break;
-    case 2: rc = go(landscape_kernel<2>); break;
-    default: rc = go(landscape_kernel<3>); break;
+    TREX_LS_CASE(0)
+    TREX_LS_CASE(1)
+    TREX_LS_CASE(2)
+    default:
+      rc = n_states == 4 ? go(landscape_kernel<3, 4>) : n_states == 20 ? go(landscape_kernel<3, 20>) : go(landscape_kernel<3, 0>);
+      break;
   }
+#undef TREX_LS_CASE
   if (rc) return rc;
   if (out_fitness_cost) {
     landscape_final_kernel<<<1, 1, 0, s>>>(acc_scratch, out_fitness_cost);
