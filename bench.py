@@ -174,7 +174,8 @@ def workload_config(args, sites_per_rank):
                       "relaxed fwd + bwd (T=1), site-sharded",
           "n_leaves": N_LEAVES, "n_states": N_STATES, "n_sites_total_c5": N_SITES,
           "sites_per_rank": int(sites_per_rank), "parallelism": f"sites{args.gpus}",
-          "l2": "inputs_exceed_l2 (tables are GBs per pass; no explicit flush)"}
+          "l2": "inputs_exceed_l2 (tables are GBs per pass; no explicit flush)",
+          "step_streams": 2 if sites_per_rank <= args.overlap_below else 1}
 
 
 # ----------------------------------------------------------------------------------------------
@@ -402,7 +403,32 @@ def run_gpu(args):
   packed_h = torch.empty(2 + 2 * A * A, dtype=torch.float64).pin_memory()
   names = ["plan", "hard_fwd", "hard_bwd", "soft_fwd", "soft_bwd", "reduce"]
 
+  # Short alignments (a GPU's share under strong scaling) leave SMs idle in the top part of every walk and
+  # in the wave tails: there the hard pass and the relaxed pass, which are independent, run on two streams.
+  # (No gain at 100k sites per GPU — 15.13 vs 15.06 ms — so the long-alignment step stays on one stream and
+  # keeps its per-kernel event timings; with two streams the per-kernel times come from a serial pass.)
+  two_streams = L <= args.overlap_below
+  stream_a, stream_b = (torch.cuda.Stream(), torch.cuda.Stream()) if two_streams else (None, None)
+
+  def step_two_streams():
+    main = torch.cuda.current_stream()
+    eng.set_adjacency(adj_d)
+    stream_a.wait_stream(main)
+    stream_b.wait_stream(main)
+    with torch.cuda.stream(stream_a):
+      eng.hard_forward(cost_d, want_argmin=True)
+      eng.traceback(want_hist=True)
+    with torch.cuda.stream(stream_b):
+      eng.soft_forward(cost_d, SOFT_T)
+      eng.soft_backward(cost_d, SOFT_T, want_dleaf=True, want_dcost=True)
+    main.wait_stream(stream_a)
+    main.wait_stream(stream_b)
+    reducer([eng.total, eng.soft_total, eng.dcost, eng.edge_hist])
+
   def step(ev=None):
+    if two_streams and ev is None:
+      return step_two_streams()
+
     def mark(i):
       if ev is not None:
         ev[i].record()
@@ -441,12 +467,16 @@ def run_gpu(args):
   launches0 = int(lib.trex_kernel_launches())
   e0.record()
   for k in range(args.steps):
-    step(evs[k])
+    step(None if two_streams else evs[k])
   e1.record()
   barrier()
   # kernels of libtrex_b200.so launched in the timed region, counted by the library itself (the
   # device-side dispatch launches every candidate kernel of an operator; all but one return at once)
   gpu_launches = int(lib.trex_kernel_launches()) - launches0
+  if two_streams:  # per-kernel times of the same work, one stream (outside the timed region)
+    for k in range(args.steps):
+      step(evs[k])
+    torch.cuda.synchronize()
   ms_total = e0.elapsed_time(e1)
   clocks = sampler.stop() if rank == 0 else None
   kern_ms = {nm: float(np.mean([evs[k][i].elapsed_time(evs[k][i + 1]) for k in range(args.steps)]))
@@ -587,6 +617,8 @@ def main():
   ap.add_argument("--sites", type=int, default=0, help="override sites per rank (testing)")
   ap.add_argument("--cpu-sites", type=int, default=4096, help="sites of the bounded cpu_baseline sample")
   ap.add_argument("--ref-sites", type=int, default=2048, help="sites per step of --impl reference")
+  ap.add_argument("--overlap-below", type=int, default=50000,
+                  help="sites per rank at or below which the hard and relaxed passes run on two streams")
   ap.add_argument("--no-extras", action="store_true", help="skip tree_cost and cpu_baseline legs")
   args = ap.parse_args()
   quiet_stdout()

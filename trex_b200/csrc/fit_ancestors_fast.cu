@@ -134,8 +134,12 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
   const float b1 = 0.9f, b2 = 0.999f;
   double pw1 = pow((double)b1, (double)p.count0), pw2 = pow((double)b2, (double)p.count0);  // b^t, kept running
 
+#ifdef TREX_FIT_PROFILE  // per-phase cycle counts of tools/fit_probe.py (build with -DTREX_FIT_PROFILE, run with TREX_FIT_DEBUG=16)
   long long prof[6] = {0, 0, 0, 0, 0, 0}, tk = clock64();
   auto tick = [&](int k) { if (p.debug & 16) { const long long t = clock64(); prof[k] += t - tk; tk = t; } };
+#else
+  auto tick = [](int) {};
+#endif
   for (int it = 0; it < p.n_iter; ++it) {
     float fc = 0.f, fn = 0.f;
     for (int s0 = 0; s0 < nsites; s0 += p.tile_sites) {
@@ -313,9 +317,11 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
     __syncthreads();
     tick(5);
   }
+#ifdef TREX_FIT_PROFILE
   if ((p.debug & 16) && tid == 0 && (blockIdx.x == 0 || blockIdx.x == G - 1 || (p.debug & 32)))
     { unsigned smid; asm("mov.u32 %0, %smid;" : "=r"(smid)); printf("fit_fast sm %u cta %d cycles/iter: phaseA %lld reduce %lld publish %lld poll %lld sync %lld update %lld\n", smid, blockIdx.x,
            prof[0] / p.n_iter, prof[1] / p.n_iter, prof[2] / p.n_iter, prof[3] / p.n_iter, prof[4] / p.n_iter, prof[5] / p.n_iter); }
+#endif
 
   for (int i = tid; i < n_anc * nsites; i += NT) {
     const int a = i / nsites, s = i - a * nsites;
