@@ -81,7 +81,8 @@ TREX_API int trex_encode_leaf_states(const float* seqs, int n_leaves, int64_t n_
  *   leaf_states [n_leaves][site_stride] u8 (shared by all trees of the batch)
  *   cost        [A][A] f32
  *   dp          [batch][n_int][A][site_stride] f32 out (leaf rows are implicit)
- *   argmin      [batch][n_int][2][A][site_stride] u8 out, or NULL (score/dp only)
+ *   argmin      [batch][n_int][A][site_stride][2] u8 out, or NULL (score/dp only): the back-pointers of the two
+ *               children (slot 0 = first child) of a (state, site) are adjacent bytes
  *   root_min    [batch][site_stride] f32 out = min_s dp[root][s] per site, or NULL
  *   total       [batch] f64 out = sum over sites of root_min, or NULL */
 TREX_API int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leaves, int n_states,

@@ -39,7 +39,7 @@ def _case(kind, n, A, L, seed, cost_kind="unit", rate=0.2):
 def _native_tables(eng, tree=0):
   """dp (L,n_all,A), argmin (L,n_int,2,A) in the oracle's layout."""
   dp = eng.export_dp(tree).cpu().numpy()
-  arg = eng.argmin[tree, :, :, :, : eng.L].permute(3, 0, 1, 2).cpu().numpy()
+  arg = eng.argmin[tree, :, :, : eng.L, :].permute(2, 0, 3, 1).cpu().numpy()  # (L, n_int, slot, A)
   return dp, arg
 
 
@@ -227,7 +227,7 @@ def test_full_size_properties(n, A, L):
   rm = eng.root_min[0, :L].cpu().numpy()
   eng.hard_forward(torch.from_numpy(cost), mode=1)
   assert torch.equal(dp_fast[..., :L], eng.dp[..., :L])
-  assert torch.equal(arg_fast[..., :L], eng.argmin[..., :L])
+  assert torch.equal(arg_fast[..., :L, :], eng.argmin[..., :L, :])
   fitch = so.fitch_score(adj, states[:n], n_all, A, n)
   assert np.array_equal(rm.astype(np.int64), fitch)
   assert int(eng.total[0]) == int(fitch.sum())

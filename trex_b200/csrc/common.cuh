@@ -175,6 +175,30 @@ __device__ __forceinline__ void st_u8_stream(uint8_t* __restrict__ p, const int 
   }
 }
 
+// ---- back-pointer (argmin) table: [tree][k][state][site][slot] u8 --------------------------------
+// The two children's back-pointers of a (state, site) are adjacent bytes: the forward kernels store the 2V
+// bytes of a lane with ONE 16/32/64-bit store per state row (128 B per warp and row at V = 2 instead of two
+// 64 B rows), and the traceback fetches both children's pointers with one 16-bit load.
+// p points at (state row, site0, slot 0); a / b are the indices of the two children, a_is_slot0 says which
+// of them is the first child (slot 0 = first child, sankoff.py:80-83).
+template <int V>
+__device__ __forceinline__ void st_arg_pair(uint8_t* __restrict__ p, const int (&a)[V], const int (&b)[V],
+                                            bool a_is_slot0) {
+  if constexpr (V == 1) {
+    const unsigned w = __byte_perm((unsigned)a[0], (unsigned)b[0], a_is_slot0 ? 0x0040u : 0x0004u);
+    __stcs(reinterpret_cast<unsigned short*>(p), (unsigned short)w);
+  } else if constexpr (V == 2) {
+    const unsigned pa = (unsigned)a[0] | ((unsigned)a[1] << 8), pb = (unsigned)b[0] | ((unsigned)b[1] << 8);
+    __stcs(reinterpret_cast<unsigned*>(p), __byte_perm(pa, pb, a_is_slot0 ? 0x5140u : 0x1504u));
+  } else {
+    const unsigned pa = (unsigned)a[0] | ((unsigned)a[1] << 8) | ((unsigned)a[2] << 16) | ((unsigned)a[3] << 24);
+    const unsigned pb = (unsigned)b[0] | ((unsigned)b[1] << 8) | ((unsigned)b[2] << 16) | ((unsigned)b[3] << 24);
+    const unsigned lo = __byte_perm(pa, pb, a_is_slot0 ? 0x5140u : 0x1504u);
+    const unsigned hi = __byte_perm(pa, pb, a_is_slot0 ? 0x7362u : 0x3726u);
+    __stcs(reinterpret_cast<uint2*>(p), make_uint2(lo, hi));
+  }
+}
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

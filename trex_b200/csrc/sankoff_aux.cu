@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
   const long long site0 = ((long long)blockIdx.x * THREADS + threadIdx.x) * V;
   if (site0 < p.n_sites) {
     const float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
-    const uint8_t* arg = p.arg + (size_t)tree * n_int * 2 * A * p.stride + site0;
+    const uint8_t* arg = p.arg + ((size_t)tree * n_int * A * p.stride + site0) * 2;
     uint8_t* anc = p.anc + (size_t)tree * n_int * p.stride + site0;
     const uint8_t* leaf = p.leaf + site0;
     const Walk wk = make_walk(plan, p.phase, blockIdx.z);
@@ -87,14 +87,23 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
       ld_u8<V>(anc + (size_t)k * p.stride, st);
 #pragma unroll
       for (int v = 0; v < V; ++v) st[v] = min(st[v], A - 1);  // pad lanes may hold anything
+      // both children's back-pointers of (state, site) are one 16-bit word
+      const int ch0 = __ldg(plan.child(0) + k), ch1 = __ldg(plan.child(1) + k);
+      unsigned pair[V];
+#pragma unroll
+      for (int v = 0; v < V; ++v) pair[v] = 0;
+      if (ch0 >= p.n_leaves || ch1 >= p.n_leaves) {
+#pragma unroll
+        for (int v = 0; v < V; ++v)
+          pair[v] = __ldcs(reinterpret_cast<const unsigned short*>(arg + (((size_t)k * A + st[v]) * p.stride + v) * 2));
+      }
 #pragma unroll
       for (int slot = 0; slot < 2; ++slot) {
-        const int c = __ldg(plan.child(slot) + k);
+        const int c = slot ? ch1 : ch0;
         int cs[V];
         if (c >= p.n_leaves) {
 #pragma unroll
-          for (int v = 0; v < V; ++v)
-            cs[v] = __ldcs(arg + (((size_t)k * 2 + slot) * A + st[v]) * p.stride + v);
+          for (int v = 0; v < V; ++v) cs[v] = (int)((pair[v] >> (8 * slot)) & 0xffu);
           st_u8<V>(anc + (size_t)(c - p.n_leaves) * p.stride, cs);
         } else if (c >= 0 && p.hist) {
           ld_u8<V>(leaf + (size_t)c * p.stride, cs);
@@ -170,8 +179,8 @@ __global__ void export_bt_kernel(const int32_t* __restrict__ plan, int n_all, in
     PlanView pv(plan, n_int);
     v.x = (float)pv.raw(0)[k];
     v.z = (float)pv.raw(1)[k];
-    v.y = (float)arg[(((size_t)k * 2 + 0) * A + s) * stride + l];
-    v.w = (float)arg[(((size_t)k * 2 + 1) * A + s) * stride + l];
+    v.y = (float)arg[(((size_t)k * A + s) * stride + l) * 2 + 0];
+    v.w = (float)arg[(((size_t)k * A + s) * stride + l) * 2 + 1];
   }
   reinterpret_cast<float4*>(out)[(size_t)l * n_all * A + j] = v;
 }

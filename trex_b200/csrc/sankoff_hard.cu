@@ -5,7 +5,7 @@
 // Replaces run_dp / vectorized_dp and the table + score part of run_sankoff
 // (src/trex/sankoff.py:24-97, 141-160, 187).
 //
-// HBM layout: dp[tree][k][state][site] f32, argmin[tree][k][slot][state][site] u8, leaf states
+// HBM layout: dp[tree][k][state][site] f32, argmin[tree][k][state][site][slot] u8, leaf states
 // [leaf][site] u8.  Leaf dp rows (1e5 with a 0 at the observed state, :49-52,152) are never
 // materialised: min_t(C[s,t] + leafrow[t]) is a (A+1) x A lookup table in shared memory built
 // with exactly the reference's f32 arithmetic (row A = "no state": all-1e5).
@@ -135,10 +135,7 @@ __device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long lo
 #pragma unroll
     for (int v = 0; v < V; ++v) o[v] = b0[v] + b1[v];  // (0 + cost0) + cost1, sankoff.py:70
     st_f<V>(out + (size_t)s * stride, o);
-    if (arg_out) {
-      st_u8_stream<V>(arg_out + (size_t)s * stride, i0);
-      st_u8_stream<V>(arg_out + ((size_t)A + s) * stride, i1);
-    }
+    if (arg_out) st_arg_pair<V>(arg_out + (size_t)s * 2 * stride, i0, i1, true);
     if (is_root) {
 #pragma unroll
       for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], o[v]);
@@ -193,7 +190,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
 
   if (active) {
     float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
-    uint8_t* arg = p.arg ? p.arg + (size_t)tree * n_int * 2 * A * p.stride + site0 : nullptr;
+    uint8_t* arg = p.arg ? p.arg + ((size_t)tree * n_int * A * p.stride + site0) * 2 : nullptr;
     const uint8_t* leaf = p.leaf + site0;
     const int32_t* order = plan.order();
     const int32_t* ch0 = plan.child(0);

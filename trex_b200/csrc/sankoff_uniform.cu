@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
 
   if (active) {
     float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
-    uint8_t* arg = WANT_ARG ? p.arg + (size_t)tree * n_int * 2 * A * stride + site0 : nullptr;
+    uint8_t* arg = WANT_ARG ? p.arg + ((size_t)tree * n_int * A * stride + site0) * 2 : nullptr;
     const uint8_t* leaf = p.leaf + site0;
     const int32_t* order = wk.ord;
     const int32_t* ch0 = plan.child(0);
@@ -192,14 +192,10 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
       row_first_min<AP, V, WANT_ARG>(dx, a, amx, jx);
       row_first_min<AP, V, WANT_ARG>(dy, a, amy, jy);
       float* out = dp + (size_t)k * A * stride;
-      // argmin slot of child x / child y (slot 0 = first child, sankoff.py:80-83)
-      uint8_t* aout_x = nullptr;
-      uint8_t* aout_y = nullptr;
-      if (WANT_ARG) {
-        uint8_t* aout = arg + (size_t)k * 2 * A * stride;
-        aout_x = aout + (x_is_0 ? 0 : (size_t)A * stride);
-        aout_y = aout + (x_is_0 ? (size_t)A * stride : 0);
-      }
+      // back-pointers of child x / child y, interleaved per site (slot 0 = first child, sankoff.py:80-83);
+      // x_first is taken NOW: decode(i + 1) below overwrites x_is_0 with the next node's
+      uint8_t* aout = WANT_ARG ? arg + (size_t)k * 2 * A * stride : nullptr;
+      const bool x_first = x_is_0;
       // the next node (its leaf states are fetched now, its dy rows inside the state loop)
       prev = node;
       const bool more = i + 1 < n_walk;
@@ -220,10 +216,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
             dx[s][v] = fminf(dx[s][v], amx[v]) + fminf(dy[s][v], amy[v]);
           }
           st_f<V>(out + (size_t)s * stride, dx[s]);
-          if (WANT_ARG) {
-            st_u8_stream<V>(aout_x + (size_t)s * stride, ix);
-            st_u8_stream<V>(aout_y + (size_t)s * stride, iy);
-          }
+          if (WANT_ARG) st_arg_pair<V>(aout + (size_t)s * 2 * stride, ix, iy, x_first);
           if (reload) ld_f<V>(nsrc + (size_t)s * stride, dy[s]);
         }
       });

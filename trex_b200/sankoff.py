@@ -27,7 +27,7 @@ class SankoffEngine:
   """Buffers + kernels for one (n_all, n_leaves, A, L, batch) problem shape.
 
   Native layouts (see include/trex_b200.h): ``leaf`` u8 [n_leaves][stride];
-  ``dp``/``gbar`` f32 [batch][n_int][A][stride]; ``argmin`` u8 [batch][n_int][2][A][stride];
+  ``dp``/``gbar`` f32 [batch][n_int][A][stride]; ``argmin`` u8 [batch][n_int][A][stride][2] (slot last);
   ``anc`` u8 [batch][n_int][stride].  Buffers are created lazily, once.
   """
 
@@ -66,7 +66,7 @@ class SankoffEngine:
 
   @property
   def argmin(self):
-    return self.buf("argmin", (self.batch, self.n_int, 2, self.A, self.stride), torch.uint8)
+    return self.buf("argmin", (self.batch, self.n_int, self.A, self.stride, 2), torch.uint8)
 
   @property
   def anc(self):
@@ -121,7 +121,8 @@ class SankoffEngine:
     blk._pad_owner = hi == self.L  # only the last block may touch the pad columns of the row pitch
     blk._bufs = {"plan": self.plan}
     for name in self._SITE_TABLES:
-      blk._bufs[name] = getattr(self, name)[..., lo:]
+      t = getattr(self, name)
+      blk._bufs[name] = t[..., lo:, :] if name == "argmin" else t[..., lo:]
     return blk
 
   def site_blocks(self, n_blocks: int):
