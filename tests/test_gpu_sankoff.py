@@ -355,3 +355,33 @@ def test_site_blocks_add_up_to_the_whole_alignment():
   assert torch.equal(tot["total"], ref["total"]) and torch.equal(tot["edge_hist"], ref["edge_hist"])
   assert abs(float(tot["soft_total"]) - float(ref["soft_total"])) <= 1e-9 * abs(float(ref["soft_total"]))
   assert torch.allclose(tot["dcost"], ref["dcost"], rtol=1e-9, atol=0)
+
+
+@pytest.mark.parametrize("A,ck", [(20, "unit"), (4, "unit3"), (5, "unit")])
+def test_stateless_leaves_take_the_exact_back_pointer_path(A, ck):
+  """Leaves without a state (code >= A: the reference's dropped scatter, sankoff.py:50 -> an all-1e5 row) push
+  a + min above 2^17, where the one-compare back-pointer keys of the uniform kernel are no longer exact: warps
+  holding such a site must fall back to the three-compare rule.  Sites with 0, 1, 2 and many stateless leaves
+  are mixed, so neighbouring warps take different paths; dp and back-pointers stay bit-exact."""
+  torch = _torch()
+  from trex_b200.sankoff import SankoffEngine
+
+  n, L = 32, 300
+  adj, cost, states, _ = _case("random", n, A, L, seed=77 + A, cost_kind=ck)
+  rng = np.random.default_rng(5)
+  st = states[:n].copy()
+  for l in range(L):
+    k = [0, 1, 2, 3, 8, 20][l % 6]
+    st[rng.choice(n, size=k, replace=False), l] = 255 if l % 2 else A
+  n_all = 2 * n - 1
+  seqs = st.astype(np.float32)
+  tabs = so.run_sankoff_tables(adj, cost, seqs, n_all, A, n)
+  eng = SankoffEngine(n_all, n, A, L)
+  eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(st))
+  eng.hard_forward(torch.from_numpy(cost))
+  dp, arg = _native_tables(eng)
+  assert np.array_equal(dp, tabs["dp"])
+  assert np.array_equal(arg, tabs["argmin"][:, n:].astype(np.uint8))
+  eng.traceback()
+  want = so.traceback_topdown(tabs, n_all, n)
+  assert np.array_equal(eng.anc[0, :, :L].cpu().numpy(), want[n:].astype(np.uint8))

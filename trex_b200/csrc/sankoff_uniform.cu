@@ -82,6 +82,23 @@ __device__ __forceinline__ int pick_index(float d, float am, int j) {
   return idx;
 }
 
+// The same decision with ONE compare when the scores are small integers (they are integers whenever this
+// kernel runs: hard_uniform_applies demands an integral cost, and leaf rows are 0 / 1e5): with
+// key(d, s) = d + s/64, exact for am < 2^17, "self wins" <=> key(d, S) <= key(am, j).  d itself may be large
+// (a lineage of stateless leaves): rounding is monotone, so a d >= 2^18 still compares above any valid key.
+// The add runs on the FMA pipe; the ALU pipe — the one this kernel saturates — sees FSETP + SEL instead of
+// three SETPs + SEL.
+template <int S>
+__device__ __forceinline__ int pick_index_key(float d, float keyj, int j) {
+  int idx;
+  asm("{\n\t.reg .pred p;\n\t.reg .f32 k;\n\t"
+      "add.f32 k, %1, %2;\n\t"
+      "setp.le.f32 p, k, %3;\n\t"
+      "selp.s32 %0, %4, %5, p;\n\t}"
+      : "=r"(idx) : "f"(d), "f"((float)S * 0.015625f), "f"(keyj), "n"(S), "r"(j));
+  return idx;
+}
+
 // A rows of a dp node, state-major
 template <int AP, int V, bool FULL>
 __device__ __forceinline__ void load_rows(const float* __restrict__ src, int A, size_t stride, float (&d)[AP][V]) {
@@ -146,6 +163,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
   float rmin[V];
 #pragma unroll
   for (int v = 0; v < V; ++v) rmin[v] = INFINITY;
+  const unsigned walkers = __ballot_sync(0xffffffffu, active);  // the lanes of this warp that walk the tree
 
   if (active) {
     float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
@@ -202,6 +220,17 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
       if (more) decode(i + 1);
       const bool reload = more && cy >= p.n_leaves;
       const float* nsrc = dp + (size_t)(reload ? cy - p.n_leaves : 0) * A * stride;
+      // one-compare back-pointers when every lane's a + min is a small integer (warp-uniform choice)
+      bool small = WANT_ARG;
+      float kjx[V], kjy[V];
+#pragma unroll
+      for (int v = 0; v < V; ++v) {
+        small = small && amx[v] < 131072.f && amy[v] < 131072.f;
+        kjx[v] = fmaf((float)jx[v], 0.015625f, amx[v]);
+        kjy[v] = fmaf((float)jy[v], 0.015625f, amy[v]);
+      }
+      small = WANT_ARG && __all_sync(walkers, small);
+      auto state_rows = [&](auto keyed) {
       static_for<AP>([&](auto sc) {
         constexpr int s = decltype(sc)::value;
         if (FULL || s < A) {
@@ -209,8 +238,13 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
 #pragma unroll
           for (int v = 0; v < V; ++v) {
             if (WANT_ARG) {
-              ix[v] = pick_index<s>(dx[s][v], amx[v], jx[v]);
-              iy[v] = pick_index<s>(dy[s][v], amy[v], jy[v]);
+              if constexpr (decltype(keyed)::value) {
+                ix[v] = pick_index_key<s>(dx[s][v], kjx[v], jx[v]);
+                iy[v] = pick_index_key<s>(dy[s][v], kjy[v], jy[v]);
+              } else {
+                ix[v] = pick_index<s>(dx[s][v], amx[v], jx[v]);
+                iy[v] = pick_index<s>(dy[s][v], amy[v], jy[v]);
+              }
             }
             // (0 + cost0) + cost1, sankoff.py:70 (f32 addition commutes)
             dx[s][v] = fminf(dx[s][v], amx[v]) + fminf(dy[s][v], amy[v]);
@@ -220,6 +254,9 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
           if (reload) ld_f<V>(nsrc + (size_t)s * stride, dy[s]);
         }
       });
+      };
+      if (small) state_rows(std::true_type{});
+      else state_rows(std::false_type{});
     }
     // per-site root minimum (sankoff.py:187): the root's row is still in dx unless nodes the root does
     // not reach followed it in the walk
