@@ -566,6 +566,10 @@ def run_gpu(args):
                    "peak_source": peak_src, "unit": "GB/s", "frac": roof_all[dom]["frac"], "traffic": traffic,
                    "note": "achieved = SURVEY 8(d) algorithmic bytes / CUDA-event launch time on the launching stream"},
       "roofline_all": roof_all,
+      "roofline_step": {"bound": "hbm", "alg_bytes": sum(per_site.values()) * L,
+                        "achieved": sum(per_site.values()) * L / (ms_total / args.steps * 1e-3) / 1e9, "peak": peak,
+                        "unit": "GB/s", "frac": sum(per_site.values()) * L / (ms_total / args.steps * 1e-3) / 1e9 / peak,
+                        "note": "all four passes of the step: SURVEY 8(d) algorithmic bytes / step time"},
       "kernel_ms": kern_ms,
       "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
               "h2d_bytes_per_step": int(states_p.numel() + adj_p.numel() * 4 + cost_p.numel() * 4),
