@@ -199,7 +199,9 @@ TREX_API int trex_compute_cost(const float* seqs_one_hot, const float* adjacency
  *   optimizer: TREX_OPT_*; clip_norm <= 0 disables clipping; step_count = updates already applied (bias correction)
  *   out_losses [n_iterations] f32 or NULL (loss BEFORE each update, as lax.scan returns them, :176-188)
  *   out_argmax [n_anc][L] i32 or NULL (jnp.argmax(ancestors, -1) after the last update, :200)
- *   workspace: trex_fit_ancestors_workspace_bytes(...) bytes.  n_anc <= 128 (else TREX_ERR_UNSUPPORTED). */
+ *   workspace: trex_fit_ancestors_workspace_bytes(...) bytes.  Limits (else TREX_ERR_UNSUPPORTED): with 4 or 20
+ *   states up to 4096 ancestors as long as one site of all ancestors fits in shared memory (n_anc * n_states
+ *   * 4 B + 64 B * n_anc <= 220 KB: 1023 ancestors at 20 states do); other alphabets: n_anc <= 128. */
 #define TREX_OPT_ADAM 0
 #define TREX_OPT_SGD 1
 #define TREX_OPT_RMSPROP 2

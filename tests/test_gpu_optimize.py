@@ -82,6 +82,24 @@ def test_each_optimizer_matches_oracle(name, kernel_path):
   assert np.linalg.norm(x - ref_x) <= 2e-4 * np.linalg.norm(ref_x - init)
 
 
+@pytest.mark.parametrize("n,L,Q,soft", [(200, 40, 4, False), (200, 24, 4, True), (160, 9, 20, False)])
+def test_more_than_128_ancestors(n, L, Q, soft):
+  """Beyond 128 ancestors A2[anc, anc] no longer fits in shared memory: the sparse (tree) product runs from the
+  ELL form, the dense (soft adjacency) product reads A2 through L2."""
+  import torch
+  from oracle import optimize_oracle as oo
+  from trex_b200 import optimize as O
+
+  leaf, N, adj, init = _problem(n, L, Q, 1000 + n, soft_adj=soft)
+  _, ref_losses, ref_x = oo.run_trex_optimization_configurable(leaf, N, n, Q, adj, init, "adam", 0.05, 4)
+  fit = O.AncestorFit(leaf, N, n, Q, adj, init, O.create_optimizer("adam", 0.05))
+  losses = torch.empty(4, device="cuda")
+  fit.run(4, losses)
+  assert np.abs(losses.cpu().numpy() - ref_losses).max() <= RTOL * np.abs(ref_losses).max()
+  x = fit.logits.cpu().numpy().astype(np.float64)
+  assert np.linalg.norm(x - ref_x) <= 1e-4 * np.linalg.norm(ref_x - init)
+
+
 def test_no_clipping_and_continuation(kernel_path):
   import torch
   from oracle import optimize_oracle as oo

@@ -339,7 +339,7 @@ FitLayout fit_layout(int N, int n_leaves, long long L, int Q) {
   f.sites_per_cta = (int)((L + g - 1) / g);
   f.grid = (int)((L + f.sites_per_cta - 1) / f.sites_per_cta);
   const size_t budget = 220 * 1024;
-  f.fast = (Q == 4 || Q == 20) && n_anc <= kMaxAnc;
+  f.fast = (Q == 4 || Q == 20) && n_anc <= kMaxAncFast;
   if (const char* e = getenv("TREX_FIT_PATH")) {  // tests: "generic" forces the scalar kernel
     if (e[0] == 'g') f.fast = 0;
   }
@@ -406,11 +406,12 @@ int trex_fit_ancestors(const float* adjacency, const float* leaf_seqs, int n_nod
   TREX_CHECK_ARG(optimizer >= OPT_ADAM && optimizer <= OPT_ADAMW, "trex_fit_ancestors: unknown optimizer %d", optimizer);
   TREX_CHECK_ARG(n_iterations >= 0 && step_count >= 0, "trex_fit_ancestors: negative iteration count");
   const int n_anc = n_nodes - n_leaves;
-  if (n_anc > kMaxAnc) {
-    set_error("trex_fit_ancestors: %d ancestors > %d (A2[anc, anc] must fit in shared memory)", n_anc, kMaxAnc);
+  const FitLayout f = fit_layout(n_nodes, n_leaves, n_sites, n_states);
+  if (n_anc > (f.fast ? kMaxAncFast : kMaxAnc) || f.smem > 225 * 1024) {
+    set_error("trex_fit_ancestors: %d ancestors x %d states does not fit (limit %d ancestors for 4 / 20 states, %d "
+              "otherwise)", n_anc, n_states, kMaxAncFast, kMaxAnc);
     return TREX_ERR_UNSUPPORTED;
   }
-  const FitLayout f = fit_layout(n_nodes, n_leaves, n_sites, n_states);
   char* ws = (char*)workspace;
   FitParams p{};
   p.a2 = (const float*)(ws + f.a2);

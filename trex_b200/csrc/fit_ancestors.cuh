@@ -7,7 +7,8 @@ namespace trex {
 namespace fit {
 
 constexpr int kThreads = 256;
-constexpr int kMaxAnc = 128;   // A2[anc, anc] lives in shared memory
+constexpr int kMaxAnc = 128;   // up to here A2[anc, anc] is staged in shared memory (generic kernel: hard limit)
+constexpr int kMaxAncFast = 4096;  // fast kernel beyond kMaxAnc: ELL from shared memory, or the dense A2 read from L2
 constexpr int kTileCols = 64;  // columns (sites x states) of one product tile of the generic kernel
 constexpr int kEll = 8;        // a row of A2[anc, anc] with at most this many non-zeros is "sparse" (a tree has <= 4)
 constexpr int kFastThreads = 512;

@@ -75,10 +75,12 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
   extern __shared__ __align__(16) float smem[];
   __shared__ double red[2 * NW + 2];
   const int n_anc = p.n_anc;
-  const int lda = (n_anc + 3) & ~3;
+  const bool big = n_anc > kMaxAnc;  // no room for the dense A2[anc, anc]: read it from global memory (L2)
+  const int lda = big ? p.N : (n_anc + 3) & ~3;
   const int ldt = p.tile_sites * Q;
-  float* sA = smem;                                               // [n_anc][lda]   dense A2[anc, anc]
-  int* sIdx = reinterpret_cast<int*>(sA + (size_t)n_anc * lda);   // [n_anc][kEll]
+  float* sA_smem = smem;                                          // [n_anc][lda]   dense A2[anc, anc] (!big)
+  const float* sA = big ? p.a2 + (size_t)p.n_leaves * p.N + p.n_leaves : sA_smem;
+  int* sIdx = reinterpret_cast<int*>(sA_smem + (big ? 0 : (size_t)n_anc * lda));   // [n_anc][kEll]
   float* sVal = reinterpret_cast<float*>(sIdx + n_anc * kEll);    // [n_anc][kEll]
   float* sS = sVal + n_anc * kEll;                                // [n_anc][ldt]   softmax of the tile
   float* sRes = sS + (size_t)n_anc * ldt;                         // resident state, [n_anc][ldc] each
@@ -123,10 +125,10 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
   }
   if (sparse) {
     for (int i = tid; i < n_anc * kEll; i += NT) { sIdx[i] = p.ell_idx[i]; sVal[i] = p.ell_val[i]; }
-  } else {
+  } else if (!big) {
     for (int i = tid; i < n_anc * lda; i += NT) {
       const int b = i / lda, a = i - b * lda;
-      sA[i] = a < n_anc ? p.a2[(size_t)(p.n_leaves + b) * p.N + p.n_leaves + a] : 0.f;
+      sA_smem[i] = a < n_anc ? p.a2[(size_t)(p.n_leaves + b) * p.N + p.n_leaves + a] : 0.f;
     }
   }
   __syncthreads();
@@ -351,7 +353,7 @@ __global__ void __launch_bounds__(NT, 1) fit_fast_kernel(const FitParams p) {
 
 size_t fit_fast_smem(int n_anc, int Q, int sites_per_cta, int tile_sites, int n_resident) {
   const int lda = (n_anc + 3) & ~3;
-  size_t fl = (size_t)n_anc * lda + 2 * (size_t)n_anc * kEll + (size_t)n_anc * tile_sites * Q;
+  size_t fl = (n_anc > kMaxAnc ? 0 : (size_t)n_anc * lda) + 2 * (size_t)n_anc * kEll + (size_t)n_anc * tile_sites * Q;
   fl += (size_t)n_resident * n_anc * sites_per_cta * Q;
   return fl * sizeof(float);
 }
