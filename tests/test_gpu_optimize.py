@@ -82,7 +82,8 @@ def test_each_optimizer_matches_oracle(name, kernel_path):
   assert np.linalg.norm(x - ref_x) <= 2e-4 * np.linalg.norm(ref_x - init)
 
 
-@pytest.mark.parametrize("n,L,Q,soft", [(200, 40, 4, False), (200, 24, 4, True), (160, 9, 20, False)])
+@pytest.mark.parametrize("n,L,Q,soft", [(200, 40, 4, False), (200, 24, 4, True), (160, 9, 20, False),
+                                        (1024, 48, 20, False)])  # the last: the c5 tree, 1023 ancestors
 def test_more_than_128_ancestors(n, L, Q, soft):
   """Beyond 128 ancestors A2[anc, anc] no longer fits in shared memory: the sparse (tree) product runs from the
   ELL form, the dense (soft adjacency) product reads A2 through L2."""
