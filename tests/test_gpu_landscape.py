@@ -41,7 +41,8 @@ def test_matches_reference_golden(name):
 
 
 @pytest.mark.parametrize("n,L,Q,k,masked", [(64, 1000, 4, 1, False), (16, 257, 20, 1, True), (8, 40, 20, 2, True),
-                                              (8, 33, 4, 3, False), (4, 3, 3, 2, True)])
+                                              (8, 33, 4, 3, False), (4, 3, 3, 2, True),
+                                              (4, 4, 20, 3, False)])  # the last: a 640 KB table per site, read from L2
 def test_value_and_gradients_match_float64_oracle(n, L, Q, k, masked):
   import torch
   from oracle import landscape_oracle as lo
