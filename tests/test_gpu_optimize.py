@@ -153,5 +153,9 @@ def test_reference_signature_and_errors():
   out2, losses = O.run_trex_optimization_configurable(leaf, N, n, Q, adj, 123, optimizer_name="sgd",
                                                       learning_rate=0.1, n_iterations=5, return_losses=True)
   assert losses.shape == (5,) and bool(torch.isfinite(losses).all())
+  out3 = O.run_trex_optimization_batched(leaf, N, n, Q, adj, 0, n_iterations=3, init_ancestors=init)
+  ref3 = O.run_trex_optimization_configurable(leaf, N, n, Q, adj, 0, learning_rate=1e-3, n_iterations=3,
+                                              init_ancestors=init)
+  assert torch.equal(out3, ref3)  # evals/benchmark.py:496: the batched twin is adam(1e-3) + clip(1.0)
   with pytest.raises(ValueError):
     O.create_optimizer("lion", 1e-3)  # evals/benchmark.py:64-65

@@ -102,3 +102,13 @@ def run_trex_optimization_configurable(leaf_sequences, n_all, n_leaves, n_states
   losses = torch.empty((int(n_iterations),), dtype=torch.float32, device="cuda") if return_losses else None
   out = fit.run(n_iterations, losses)
   return (out, losses) if return_losses else out
+
+
+def run_trex_optimization_batched(leaf_sequences, n_all, n_leaves, n_states, adj_matrix, key,
+                                  use_soft_cost=False, n_iterations=10000, *, init_ancestors=None):
+  """evals/benchmark.py:459-542 — the vmap-friendly twin of the loop above with its fixed optimiser
+  ``optax.chain(clip_by_global_norm(1.0), adam(1e-3))`` (:496).  Returns ``argmax (n_anc, L) int32``.
+  (The reference vmaps it over candidate trees; here each tree is one persistent kernel launch.)"""
+  return run_trex_optimization_configurable(leaf_sequences, n_all, n_leaves, n_states, adj_matrix, key,
+                                            use_soft_cost=use_soft_cost, optimizer_name="adam", learning_rate=1e-3,
+                                            n_iterations=n_iterations, init_ancestors=init_ancestors)
