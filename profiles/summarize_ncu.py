@@ -33,8 +33,12 @@ def main(rep):
     for w in WANT:
       if w in idx:
         print(f"   {w:72s} {d[idx[w]]:>22s} {units[idx[w]]}")
-    rd, wr = float(d[idx["dram__bytes_read.sum"]]), float(d[idx["dram__bytes_write.sum"]])
-    print(f"   {'traffic = dram read + write':72s} {rd + wr:22.6f} {units[idx['dram__bytes_read.sum']]}")
+    # ncu scales each launch's value on its own (Gbyte / Mbyte / Kbyte in the same column): normalise to GB
+    scale = {"byte": 1e-9, "Kbyte": 1e-6, "Mbyte": 1e-3, "Gbyte": 1.0, "Tbyte": 1e3}
+    def gb(col):
+      raw = d[idx[col]]
+      return float(raw) * scale.get(units[idx[col]], 1.0)
+    print(f"   {'traffic = dram read + write':72s} {gb('dram__bytes_read.sum') + gb('dram__bytes_write.sum'):22.6f} Gbyte")
   for name in dict.fromkeys(n.split("<")[0].split("(")[0].replace("void ", "").strip() for n in names):
     out = ncu(rep, "--page", "source", "--csv", "--kernel-name", "regex:" + name)
     rows = list(csv.reader(io.StringIO(out)))
