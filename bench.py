@@ -553,7 +553,8 @@ def run_gpu(args):
       roof_all[nm] = {"ms": kern_ms[nm], "alg_bytes": per_site[nm] * L, "achieved": gbs, "frac": gbs / peak}
     dom = max(["hard_fwd", "soft_fwd", "soft_bwd"], key=lambda k: kern_ms[k])
     # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full captures
-    # (profiles/r01_f_*_ncu_full.txt; soft_bwd re-captured at HEAD with both segment launches, profiles/r01_k_soft_bwd_uniform_ncu_full.txt:
+    # (forward kernels: profiles/r01_n_fwd_uniform_ncu_full.txt, segment + top launches: 12.22 + 0.60 and 8.24 + 0.48 GB;
+    # soft_bwd re-captured at HEAD with both segment launches, profiles/r01_k_soft_bwd_uniform_ncu_full.txt:
     # 0.98 + 24.28 GB), valid for the c5 shape at 100k sites per rank only
     ncu_traffic = {"hard_fwd": 12.79e9, "soft_fwd": 8.71e9, "soft_bwd": 25.26e9}
     traffic = ncu_traffic.get(dom) if (L == N_SITES) else None
