@@ -310,6 +310,23 @@ __device__ __forceinline__ void to_exp_domain(float (&d)[AP][V], float c1, float
   }
 }
 
+// The same for a child given by its observed state o (one-hot 1e5 row) without touching the SFU: the row is
+// 0 at o and 1e5 elsewhere, so m = 0, e[o] = 1 and e[t != o] = e_off = exp(-1e5/T) (0 unless T is huge) —
+// exactly what to_exp_domain computes from the materialised row.  o >= A (no state, an all-1e5 row): m = 1e5,
+// e = 1 everywhere.  Half of the children of a binary tree are leaves: half of the kernel's ex2.
+template <int AP, int V, bool FULL>
+__device__ __forceinline__ void leaf_exp_domain(const int (&o)[V], int A, float e_off, float kk, float (&d)[AP][V],
+                                                float (&m)[V], float (&kE)[V]) {
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const bool none = o[v] >= A;
+#pragma unroll
+    for (int t = 0; t < AP; ++t) d[t][v] = (FULL || t < A) ? ((none || o[v] == t) ? 1.f : e_off) : 0.f;
+    m[v] = none ? kSentinel : 0.f;
+    kE[v] = kk * (none ? (float)A : fmaf((float)(A - 1), e_off, 1.f));
+  }
+}
+
 }  // namespace
 
 template <int AP, int V, int THREADS, bool FULL>
@@ -328,6 +345,7 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
   const float tln2 = p.T * 0.6931471805599453f;  // T*ln(2)
   const float kk = exp2f(-a * c1);               // exp(-a/T)
   const float km1 = 1.f - kk;
+  const float e_off = ex2_approx(-kSentinel * c1);  // exp(-1e5/T): every unobserved state of a leaf row
   const size_t stride = (size_t)p.stride;
   const long long site0 = ((long long)blockIdx.x * THREADS + threadIdx.x) * V;
   const bool active = site0 < p.n_sites;
@@ -371,14 +389,12 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
       if (sy) load_rows<AP, V, FULL>(sy, A, stride, dy);
     }
     for (int i = 0; i < n_walk; ++i) {
-      if (!fwd) {
-        if (sx) load_rows<AP, V, FULL>(sx, A, stride, dx);
-        else leaf_rows<AP, V, FULL>(ox, A, dx);
-      }
-      if (!sy) leaf_rows<AP, V, FULL>(oy, A, dy);
       float mx[V], my[V], kEx[V], kEy[V];
-      to_exp_domain<AP, V>(dx, c1, kk, mx, kEx);
-      to_exp_domain<AP, V>(dy, c1, kk, my, kEy);
+      if (!fwd && sx) load_rows<AP, V, FULL>(sx, A, stride, dx);
+      if (!fwd && !sx) leaf_exp_domain<AP, V, FULL>(ox, A, e_off, kk, dx, mx, kEx);
+      else to_exp_domain<AP, V>(dx, c1, kk, mx, kEx);
+      if (!sy) leaf_exp_domain<AP, V, FULL>(oy, A, e_off, kk, dy, my, kEy);
+      else to_exp_domain<AP, V>(dy, c1, kk, my, kEy);
       float mxy[V];
 #pragma unroll
       for (int v = 0; v < V; ++v) mxy[v] = mx[v] + my[v];
