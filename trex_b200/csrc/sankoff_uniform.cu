@@ -141,6 +141,19 @@ __device__ __forceinline__ void row_first_min(const float (&d)[AP][V], float a, 
   }
 }
 
+// The same for a child given by its observed state o, whose row is 0 at o and 1e5 elsewhere: minimum 0 at o
+// (an all-1e5 row when o >= A: minimum 1e5, first at 0) — no 20-element min / first-index chain.  Half of the
+// children of a binary tree are leaves, and the kernel is bound by the ALU pipe.
+template <int V>
+__device__ __forceinline__ void leaf_first_min(const int (&o)[V], int A, float a, float (&am)[V], int (&j)[V]) {
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+    const bool none = o[v] >= A;
+    am[v] = a + (none ? kSentinel : 0.f);
+    j[v] = none ? 0 : o[v];
+  }
+}
+
 }  // namespace
 
 // FULL: n_states == AP (no padded state rows); WANT_ARG: the traceback tables are written.
@@ -200,15 +213,18 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
       if (cy >= p.n_leaves) load_rows<AP, V, FULL>(dp + (size_t)(cy - p.n_leaves) * A * stride, A, stride, dy);
     }
     for (int i = 0; i < n_walk; ++i) {
+      const bool x_leaf = !fwd && cx < p.n_leaves, y_leaf = cy < p.n_leaves;  // warp-uniform (plan data)
       if (!fwd) {
         if (cx >= p.n_leaves) load_rows<AP, V, FULL>(dp + (size_t)(cx - p.n_leaves) * A * stride, A, stride, dx);
         else leaf_rows<AP, V, FULL>(ox, A, dx);
       }
-      if (cy < p.n_leaves) leaf_rows<AP, V, FULL>(oy, A, dy);
+      if (y_leaf) leaf_rows<AP, V, FULL>(oy, A, dy);
       float amx[V], amy[V];
       int jx[V], jy[V];
-      row_first_min<AP, V, WANT_ARG>(dx, a, amx, jx);
-      row_first_min<AP, V, WANT_ARG>(dy, a, amy, jy);
+      if (x_leaf) leaf_first_min<V>(ox, A, a, amx, jx);
+      else row_first_min<AP, V, WANT_ARG>(dx, a, amx, jx);
+      if (y_leaf) leaf_first_min<V>(oy, A, a, amy, jy);
+      else row_first_min<AP, V, WANT_ARG>(dy, a, amy, jy);
       float* out = dp + (size_t)k * A * stride;
       // back-pointers of child x / child y, interleaved per site (slot 0 = first child, sankoff.py:80-83);
       // x_first is taken NOW: decode(i + 1) below overwrites x_is_0 with the next node's
