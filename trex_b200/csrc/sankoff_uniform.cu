@@ -405,6 +405,49 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwd
       if (sy) load_rows<AP, V, FULL>(sy, A, stride, dy);
     }
     for (int i = 0; i < n_walk; ++i) {
+      if (!fwd && !sx && !sy) {
+        // Both children given by their states (half of the nodes of a binary tree): e is 1 at the observed state
+        // and e_off elsewhere, so z0 z1 takes four values per site — four lg2 instead of A.  A stateless leaf
+        // (o >= A: e = 1 everywhere, m = 1e5) is the same formula with e_off -> 1.  Bit-identical to the general
+        // path: the same fmaf / product / lg2 on the same operands.
+        float l11[V], l10[V], l01[V], l00[V];
+        int lx[V], ly[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          lx[v] = ox[v];
+          ly[v] = oy[v];
+          const bool nx = ox[v] >= A, ny = oy[v] >= A;
+          const float kEx = kk * (nx ? (float)A : fmaf((float)(A - 1), e_off, 1.f));
+          const float kEy = kk * (ny ? (float)A : fmaf((float)(A - 1), e_off, 1.f));
+          const float zx1 = fmaf(km1, 1.f, kEx), zx0 = fmaf(km1, nx ? 1.f : e_off, kEx);
+          const float zy1 = fmaf(km1, 1.f, kEy), zy0 = fmaf(km1, ny ? 1.f : e_off, kEy);
+          const float mm = (nx ? kSentinel : 0.f) + (ny ? kSentinel : 0.f);
+          l11[v] = fmaf(-tln2, lg2_approx(zx1 * zy1), mm);
+          l10[v] = fmaf(-tln2, lg2_approx(zx1 * zy0), mm);
+          l01[v] = fmaf(-tln2, lg2_approx(zx0 * zy1), mm);
+          l00[v] = fmaf(-tln2, lg2_approx(zx0 * zy0), mm);
+        }
+        float* out = dp + (size_t)k * A * stride;
+        prev = node;
+        const bool more = i + 1 < n_walk;
+        if (more) decode(i + 1);
+        const bool reload = more && sy != nullptr;
+        const float* nsrc = reload ? sy : dp;
+#pragma unroll
+        for (int s = 0; s < AP; ++s) {
+          if (FULL || s < A) {
+#pragma unroll
+            for (int v = 0; v < V; ++v)
+              dx[s][v] = s == lx[v] ? (s == ly[v] ? l11[v] : l10[v]) : (s == ly[v] ? l01[v] : l00[v]);
+            st_f<V>(out + (size_t)s * stride, dx[s]);
+            if (reload) ld_f<V>(nsrc + (size_t)s * stride, dy[s]);
+          } else {
+#pragma unroll
+            for (int v = 0; v < V; ++v) dx[s][v] = dy[s][v] = INFINITY;
+          }
+        }
+        continue;
+      }
       float mx[V], my[V], kEx[V], kEy[V];
       if (!fwd && sx) load_rows<AP, V, FULL>(sx, A, stride, dx);
       if (!fwd && !sx) leaf_exp_domain<AP, V, FULL>(ox, A, e_off, kk, dx, mx, kEx);
