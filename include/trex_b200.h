@@ -144,6 +144,20 @@ TREX_API int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leaves,
                           float temperature, const float* dp, const float* gscale, float* gbar,
                           float* dleaf, double* dcost, void* stream);
 
+/* Same reverse pass for leaves given as STATE CODES, with the leaf gradient in compact form.  For such a
+ * leaf d total / d leaf_cost[leaf][t] is non-zero only at the observed state t = o (every other entry of the
+ * hard leaf row 1e5*(1-onehot) has softmin weight exp(-1e5/T) = 0), so the dense [leaf][A][site] table of
+ * trex_sankoff_soft_bwd would be (A-1)/A zeros — 7.8 of the 16.3 GB that pass writes at 1024 taxa x 100k
+ * sites x 20 states.  Here:
+ *   dleaf_obs [batch][n_leaves][site_stride] f32 out or NULL: sum_t d total / d leaf_cost[leaf][site][t]
+ *             = the entry at the observed state (for a leaf without a state: the sum over its row);
+ *             rows of leaves the root does not reach are not written. */
+TREX_API int trex_sankoff_soft_bwd_compact(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                                  int64_t n_sites, int64_t site_stride, int batch,
+                                  const uint8_t* leaf_states, const float* cost, float temperature,
+                                  const float* dp, const float* gscale, float* gbar, float* dleaf_obs,
+                                  double* dcost, void* stream);
+
 /* ---- soft-adjacency tree cost, value + gradients in one pass --------------------------------
  * Replaces compute_surrogate_cost / compute_soft_cost (src/trex/tree.py:163-209, 212-266)
  * and what jax.value_and_grad derives from them (src/trex/evals/benchmark.py:167-173).

@@ -63,3 +63,33 @@ def soft_sankoff(adj, cost, seqs, n_all, n_states, n_leaves, T, want_gbar=False)
                              C.c_int(n_leaves), C.c_long(L), C.c_float(T), C.byref(total), _p(dC),
                              _p(gbar))
   return total.value, dC, gbar
+
+
+def soft_sankoff_f64(adj, cost, n_all, n_states, n_leaves, T, seqs=None, leaf_cost=None, want_dp=True,
+                     want_gbar=True):
+  """float64 instance of the same restatement — the checker of the 1e-5 parity tests at the benchmark
+  shapes (the NumPy version needs minutes there).  Leaves: ``seqs`` (rows, L) state codes or
+  ``leaf_cost`` (n_leaves, L, A).  Returns ``(total, dC (A,A), dp (L,n_all,A) | None, gbar (L,n_all,A) | None)``."""
+  adj = np.ascontiguousarray(adj, dtype=np.float32)
+  cost = np.ascontiguousarray(cost, dtype=np.float32)
+  assert (seqs is None) != (leaf_cost is None)
+  if seqs is not None:
+    seqs = np.ascontiguousarray(seqs, dtype=np.float32)
+    L = seqs.shape[1]
+  else:
+    leaf_cost = np.ascontiguousarray(leaf_cost, dtype=np.float64)
+    L = leaf_cost.shape[1]
+  dC = np.zeros((n_states, n_states), dtype=np.float64)
+  dp = np.empty((L, n_all, n_states), dtype=np.float64) if want_dp else None
+  gbar = np.empty((L, n_all, n_states), dtype=np.float64) if want_gbar else None
+  total = C.c_double(0)
+  load().oracle_soft_sankoff_f64(_p(adj), _p(cost), _p(seqs), _p(leaf_cost), C.c_int(n_all), C.c_int(n_states),
+                                 C.c_int(n_leaves), C.c_long(L), C.c_double(T), C.byref(total), _p(dC),
+                                 _p(dp), _p(gbar))
+  return total.value, dC, dp, gbar
+
+
+def set_num_threads(n: int) -> int:
+  """OpenMP thread count of the C legs (``torch.distributed.run`` exports OMP_NUM_THREADS=1)."""
+  load().oracle_set_num_threads(C.c_int(int(n)))
+  return num_threads()

@@ -131,86 +131,116 @@ int oracle_run_sankoff(const float* adj, const float* cost, const float* seqs, i
 }
 
 /* Relaxed forward + reverse (not in the reference — restatement of :55-92 with
- * min -> -T*logsumexp(-x/T), float32 like the reference's default dtype).  Hard leaves.
- * gbar_root_only: outputs are the total, dC [A][A] f64 and (optionally) the marginals
- * gbar [L][n_all][A] f32. */
+ * min -> -T*logsumexp(-x/T)).  Hard leaves (seqs) or, when leaf_cost != NULL, a float leaf table
+ * leaf_cost [n_leaves][L][A] (REAL).  Outputs: the total, dC [A][A] f64 and (optionally) the dp table
+ * dp_out [L][n_all][A] and the cotangents / marginals gbar [L][n_all][A] (rows < n_leaves = d total /
+ * d leaf_cost).  Two instances of the same body: float32 like the reference's default dtype (the timed
+ * CPU baseline) and float64 (the checker of the 1e-5 parity tests at the benchmark shapes). */
+#define DEFINE_SOFT_SANKOFF(NAME, REAL, EXPF, LOGF)                                                      \
+  int NAME(const float* adj, const float* cost, const float* seqs, const REAL* leaf_cost, int n_all,    \
+           int A, int n_leaves, long L, REAL T, double* total, double* dC, REAL* dp_out,                \
+           REAL* gbar_out) {                                                                             \
+    int* kids = (int*)malloc(sizeof(int) * 2 * (size_t)n_all);                                           \
+    find_children(adj, n_all, 1, kids);                                                                  \
+    double tot = 0.0;                                                                                    \
+    for (int i = 0; i < A * A; ++i) dC[i] = 0.0;                                                         \
+    _Pragma("omp parallel reduction(+ : tot)") {                                                         \
+      REAL* dp = (REAL*)malloc(sizeof(REAL) * (size_t)n_all * A);                                        \
+      REAL* g = (REAL*)malloc(sizeof(REAL) * (size_t)n_all * A);                                         \
+      double* dcl = (double*)calloc((size_t)A * A, sizeof(double));                                      \
+      REAL w[64];                                                                                        \
+      _Pragma("omp for schedule(static)") for (long l = 0; l < L; ++l) {                                 \
+        for (int i = 0; i < n_all * A; ++i) dp[i] = (REAL)SENTINEL;                                      \
+        for (int i = 0; i < n_leaves; ++i) {                                                             \
+          if (leaf_cost) {                                                                               \
+            for (int s = 0; s < A; ++s) dp[i * A + s] = leaf_cost[((size_t)i * L + l) * A + s];          \
+          } else {                                                                                       \
+            int s = (int)seqs[(size_t)i * L + l];                                                        \
+            if (s < 0) s += A;                                                                           \
+            if (s >= 0 && s < A) dp[i * A + s] = (REAL)0;                                                \
+          }                                                                                              \
+        }                                                                                                \
+        for (int node = n_leaves; node < n_all; ++node) {                                                \
+          for (int s = 0; s < A; ++s) {                                                                  \
+            REAL acc = (REAL)0;                                                                          \
+            for (int k = 0; k < 2; ++k) {                                                                \
+              const int child = wrap(kids[2 * node + k], n_all);                                         \
+              const int valid = child < node;                                                            \
+              const float* c = cost + (size_t)s * A;                                                     \
+              REAL m = (REAL)INFINITY;                                                                   \
+              for (int t = 0; t < A; ++t) {                                                              \
+                w[t] = (REAL)c[t] + (valid ? dp[(size_t)child * A + t] : (REAL)SENTINEL);                \
+                if (w[t] < m) m = w[t];                                                                  \
+              }                                                                                          \
+              REAL z = (REAL)0;                                                                          \
+              for (int t = 0; t < A; ++t) z += EXPF(-(w[t] - m) / T);                                    \
+              acc += m - T * LOGF(z);                                                                    \
+            }                                                                                            \
+            dp[(size_t)node * A + s] = acc;                                                              \
+          }                                                                                              \
+        }                                                                                                \
+        const REAL* root = dp + (size_t)(n_all - 1) * A;                                                 \
+        REAL m = root[0];                                                                                \
+        for (int s = 1; s < A; ++s)                                                                      \
+          if (root[s] < m) m = root[s];                                                                  \
+        REAL z = (REAL)0;                                                                                \
+        for (int s = 0; s < A; ++s) z += EXPF(-(root[s] - m) / T);                                       \
+        tot += (double)(m - T * LOGF(z));                                                                \
+        memset(g, 0, sizeof(REAL) * (size_t)n_all * A);                                                  \
+        for (int s = 0; s < A; ++s) g[(size_t)(n_all - 1) * A + s] = EXPF(-(root[s] - m) / T) / z;       \
+        for (int node = n_all - 1; node >= n_leaves; --node) {                                           \
+          for (int k = 0; k < 2; ++k) {                                                                  \
+            const int child = wrap(kids[2 * node + k], n_all);                                           \
+            const int valid = child < node;                                                              \
+            for (int s = 0; s < A; ++s) {                                                                \
+              const REAL gs = g[(size_t)node * A + s];                                                   \
+              if (gs == (REAL)0) continue;                                                               \
+              const float* c = cost + (size_t)s * A;                                                     \
+              REAL mm = (REAL)INFINITY;                                                                  \
+              for (int t = 0; t < A; ++t) {                                                              \
+                w[t] = (REAL)c[t] + (valid ? dp[(size_t)child * A + t] : (REAL)SENTINEL);                \
+                if (w[t] < mm) mm = w[t];                                                                \
+              }                                                                                          \
+              REAL zz = (REAL)0;                                                                         \
+              for (int t = 0; t < A; ++t) {                                                              \
+                w[t] = EXPF(-(w[t] - mm) / T);                                                           \
+                zz += w[t];                                                                              \
+              }                                                                                          \
+              for (int t = 0; t < A; ++t) {                                                              \
+                const REAL contrib = gs * w[t] / zz;                                                     \
+                dcl[(size_t)s * A + t] += (double)contrib;                                               \
+                if (valid) g[(size_t)child * A + t] += contrib;                                          \
+              }                                                                                          \
+            }                                                                                            \
+          }                                                                                              \
+        }                                                                                                \
+        if (dp_out) memcpy(dp_out + (size_t)l * n_all * A, dp, sizeof(REAL) * (size_t)n_all * A);        \
+        if (gbar_out) memcpy(gbar_out + (size_t)l * n_all * A, g, sizeof(REAL) * (size_t)n_all * A);     \
+      }                                                                                                  \
+      _Pragma("omp critical") for (int i = 0; i < A * A; ++i) dC[i] += dcl[i];                           \
+      free(dp);                                                                                          \
+      free(g);                                                                                           \
+      free(dcl);                                                                                         \
+    }                                                                                                    \
+    *total = tot;                                                                                        \
+    free(kids);                                                                                          \
+    return 0;                                                                                            \
+  }
+
+DEFINE_SOFT_SANKOFF(oracle_soft_sankoff_f32, float, expf, logf)
+DEFINE_SOFT_SANKOFF(oracle_soft_sankoff_f64, double, exp, log)
+
+/* the timed CPU baseline: float32, hard leaves */
 int oracle_soft_sankoff(const float* adj, const float* cost, const float* seqs, int n_all, int A,
                         int n_leaves, long L, float T, double* total, double* dC, float* gbar_out) {
-  int* kids = (int*)malloc(sizeof(int) * 2 * (size_t)n_all);
-  find_children(adj, n_all, 1, kids);
-  double tot = 0.0;
-  for (int i = 0; i < A * A; ++i) dC[i] = 0.0;
-#pragma omp parallel reduction(+ : tot)
-  {
-    float* dp = (float*)malloc(sizeof(float) * (size_t)n_all * A);
-    float* g = (float*)malloc(sizeof(float) * (size_t)n_all * A);
-    double* dcl = (double*)calloc((size_t)A * A, sizeof(double));
-    float w[64];
-#pragma omp for schedule(static)
-    for (long l = 0; l < L; ++l) {
-      for (int i = 0; i < n_all * A; ++i) dp[i] = SENTINEL;
-      for (int i = 0; i < n_leaves; ++i) {
-        int s = (int)seqs[(size_t)i * L + l];
-        if (s < 0) s += A;
-        if (s >= 0 && s < A) dp[i * A + s] = 0.f;
-      }
-      for (int node = n_leaves; node < n_all; ++node) {
-        for (int s = 0; s < A; ++s) {
-          float acc = 0.f;
-          for (int k = 0; k < 2; ++k) {
-            const int child = wrap(kids[2 * node + k], n_all);
-            const int valid = child < node;
-            const float* c = cost + (size_t)s * A;
-            float m = INFINITY;
-            for (int t = 0; t < A; ++t) {
-              w[t] = c[t] + (valid ? dp[(size_t)child * A + t] : SENTINEL);
-              if (w[t] < m) m = w[t];
-            }
-            float z = 0.f;
-            for (int t = 0; t < A; ++t) z += expf(-(w[t] - m) / T);
-            acc += m - T * logf(z);
-          }
-          dp[(size_t)node * A + s] = acc;
-        }
-      }
-      const float* root = dp + (size_t)(n_all - 1) * A;
-      float m = root[0];
-      for (int s = 1; s < A; ++s) if (root[s] < m) m = root[s];
-      float z = 0.f;
-      for (int s = 0; s < A; ++s) z += expf(-(root[s] - m) / T);
-      tot += (double)(m - T * logf(z));
-      memset(g, 0, sizeof(float) * (size_t)n_all * A);
-      for (int s = 0; s < A; ++s) g[(size_t)(n_all - 1) * A + s] = expf(-(root[s] - m) / T) / z;
-      for (int node = n_all - 1; node >= n_leaves; --node) {
-        for (int k = 0; k < 2; ++k) {
-          const int child = wrap(kids[2 * node + k], n_all);
-          const int valid = child < node;
-          for (int s = 0; s < A; ++s) {
-            const float gs = g[(size_t)node * A + s];
-            if (gs == 0.f) continue;
-            const float* c = cost + (size_t)s * A;
-            float mm = INFINITY;
-            for (int t = 0; t < A; ++t) {
-              w[t] = c[t] + (valid ? dp[(size_t)child * A + t] : SENTINEL);
-              if (w[t] < mm) mm = w[t];
-            }
-            float zz = 0.f;
-            for (int t = 0; t < A; ++t) { w[t] = expf(-(w[t] - mm) / T); zz += w[t]; }
-            for (int t = 0; t < A; ++t) {
-              const float contrib = gs * w[t] / zz;
-              dcl[(size_t)s * A + t] += (double)contrib;
-              if (valid) g[(size_t)child * A + t] += contrib;
-            }
-          }
-        }
-      }
-      if (gbar_out) memcpy(gbar_out + (size_t)l * n_all * A, g, sizeof(float) * (size_t)n_all * A);
-    }
-#pragma omp critical
-    for (int i = 0; i < A * A; ++i) dC[i] += dcl[i];
-    free(dp); free(g); free(dcl);
-  }
-  *total = tot;
-  free(kids);
-  return 0;
+  return oracle_soft_sankoff_f32(adj, cost, seqs, NULL, n_all, A, n_leaves, L, T, total, dC, NULL, gbar_out);
+}
+
+/* thread count of the OpenMP legs (torchrun exports OMP_NUM_THREADS=1: bench.py sets it back) */
+void oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
 }

@@ -35,6 +35,7 @@ SIGNATURES = {
   "trex_sankoff_backtrack_ref": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp]),
   "trex_sankoff_soft_fwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp]),
   "trex_sankoff_soft_bwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
+  "trex_sankoff_soft_bwd_compact": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
   "trex_tree_cost_workspace_bytes": (C.c_size_t, [_i, _i64, _i]),
   "trex_tree_cost_fwd_bwd": (_i, [_vp, _vp, _vp, _i, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
   "trex_update_seq_fwd": (_i, [_vp, _i, _i64, _i, _f, _vp, _vp]),

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(THREADS) soft_bwd_kernel(const SoftBwdParams p
   const float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
   float* gbar = p.gbar + (size_t)tree * n_int * A * p.stride + site0;
   float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * p.stride + site0 : nullptr;
+  float* dleaf_obs = p.dleaf_obs ? p.dleaf_obs + (size_t)tree * p.n_leaves * p.stride + site0 : nullptr;
   const int32_t* order = plan.order();
   const int n_reach = plan.hdr()[1];
 
@@ -303,6 +304,18 @@ __global__ void __launch_bounds__(THREADS) soft_bwd_kernel(const SoftBwdParams p
           for (int t = 0; t < AP; ++t)
             if (t < A) st_f<V>(dst + (size_t)t * p.stride, gc[t]);
         }
+        if (dleaf_obs && c >= 0 && c < p.n_leaves && !p.leaf_cost) {
+          // compact leaf gradient: the whole cotangent mass of the parent lands on the leaf's row
+          // (on its observed-state entry when it has one) because the softmin weights of a row sum to 1
+          float mass[V];
+#pragma unroll
+          for (int v = 0; v < V; ++v) {
+            mass[v] = 0.f;
+#pragma unroll
+            for (int s = 0; s < AP; ++s) mass[v] += s < A ? g[s][v] : 0.f;
+          }
+          st_f<V>(dleaf_obs + (size_t)c * p.stride, mass);
+        }
       }
       if constexpr (WANT_DC) {
         if (expdom) {
@@ -380,16 +393,15 @@ static int launch_soft_bwd(const SoftBwdParams& p, int batch, cudaStream_t s) {
 
 }  // namespace trex
 
-extern "C" int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
-                                     int64_t n_sites, int64_t site_stride, int batch,
-                                     const uint8_t* leaf_states, const float* leaf_cost,
-                                     const float* cost, float temperature, const float* dp,
-                                     const float* gscale, float* gbar, float* dleaf,
-                                     double* dcost, void* stream) {
-  using namespace trex;
+namespace trex {
+static int soft_bwd_entry(const int32_t* plan, int n_all, int n_leaves, int n_states, int64_t n_sites,
+                          int64_t site_stride, int batch, const uint8_t* leaf_states, const float* leaf_cost,
+                          const float* cost, float temperature, const float* dp, const float* gscale,
+                          float* gbar, float* dleaf, float* dleaf_obs, double* dcost, void* stream) {
   TREX_CHECK_ARG(plan && cost && dp && gbar, "trex_sankoff_soft_bwd: null pointer");
   TREX_CHECK_ARG((leaf_states != nullptr) != (leaf_cost != nullptr),
                  "trex_sankoff_soft_bwd: exactly one of leaf_states / leaf_cost must be given");
+  TREX_CHECK_ARG(!(dleaf_obs && leaf_cost), "trex_sankoff_soft_bwd_compact: the compact leaf gradient needs leaf_states");
   TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves, "trex_sankoff_soft_bwd: need n_all > n_leaves >= 1");
   TREX_CHECK_ARG(n_states >= 1 && n_states <= 32, "trex_sankoff_soft_bwd: n_states %d not in 1..32", n_states);
   TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0,
@@ -403,7 +415,7 @@ extern "C" int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leave
   }
   SoftBwdParams p{plan, trex_sankoff_plan_words(n_all, n_leaves), n_all, n_leaves, n_states,
                   (long long)n_sites, (long long)site_stride, leaf_states, leaf_cost, cost,
-                  temperature, dp, gscale, gbar, dleaf, dcost, 0};
+                  temperature, dp, gscale, gbar, dleaf, dleaf_obs, dcost, 0, 0};
   const int A = n_states;
   if (A <= 20) {
     // Device-side dispatch (the cost matrix is device data): the O(A) kernel returns at once unless
@@ -420,4 +432,24 @@ extern "C" int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leave
   if (A <= 8) return launch_soft_bwd<8, 1, 256>(p, batch, s);
   if (A <= 20) return launch_soft_bwd<20, 1, 256>(p, batch, s);
   return launch_soft_bwd<32, 1, 512>(p, batch, s);
+}
+}  // namespace trex
+
+extern "C" int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                                     int64_t n_sites, int64_t site_stride, int batch,
+                                     const uint8_t* leaf_states, const float* leaf_cost,
+                                     const float* cost, float temperature, const float* dp,
+                                     const float* gscale, float* gbar, float* dleaf,
+                                     double* dcost, void* stream) {
+  return trex::soft_bwd_entry(plan, n_all, n_leaves, n_states, n_sites, site_stride, batch, leaf_states, leaf_cost,
+                              cost, temperature, dp, gscale, gbar, dleaf, nullptr, dcost, stream);
+}
+
+extern "C" int trex_sankoff_soft_bwd_compact(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                                             int64_t n_sites, int64_t site_stride, int batch,
+                                             const uint8_t* leaf_states, const float* cost, float temperature,
+                                             const float* dp, const float* gscale, float* gbar,
+                                             float* dleaf_obs, double* dcost, void* stream) {
+  return trex::soft_bwd_entry(plan, n_all, n_leaves, n_states, n_sites, site_stride, batch, leaf_states, nullptr,
+                              cost, temperature, dp, gscale, gbar, nullptr, dleaf_obs, dcost, stream);
 }

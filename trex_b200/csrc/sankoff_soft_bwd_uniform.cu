@@ -129,6 +129,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
   const float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
   float* gbar = p.gbar + (size_t)tree * n_int * A * stride + site0;
   float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * stride + site0 : nullptr;
+  float* dleaf_obs = p.dleaf_obs ? p.dleaf_obs + (size_t)tree * p.n_leaves * stride + site0 : nullptr;
   const float* leaf_cost = p.leaf_cost ? p.leaf_cost + site0 : nullptr;
   const Walk wk = make_walk(plan, p.phase, blockIdx.z);
   const int32_t* order = wk.ord;  // this launch walks order[n_reach-1] down to order[0]
@@ -405,6 +406,15 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
             for (int v = 0; v < V; ++v) out[v] = (slot ? oB[v] : oA[v]) == t ? tot[v] : 0.f;
             st_f_stream<V>(dst + (size_t)t * stride, out);
           }
+        }
+      }
+      // compact form: one value per (leaf, site) = the mass on the leaf's row (its observed-state entry)
+      if (dleaf_obs && active) {
+#pragma unroll
+        for (int slot = 0; slot < 2; ++slot) {
+          const int c = slot ? cB : cA;
+          if ((slot ? srcB : srcA) || c < 0) continue;
+          st_f_stream<V>(dleaf_obs + (size_t)c * stride, tot);
         }
       }
       if (WANT_DC) {

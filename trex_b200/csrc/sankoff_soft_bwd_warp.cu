@@ -134,6 +134,7 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   const float* dp = p.dp + (size_t)tree * n_int * A * stride + site0;
   float* gbar = p.gbar + (size_t)tree * n_int * A * stride + site0;
   float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * stride + site0 : nullptr;
+  float* dleaf_obs = p.dleaf_obs ? p.dleaf_obs + (size_t)tree * p.n_leaves * stride + site0 : nullptr;
   const int32_t* order = plan.order();
   const int32_t* ch0 = plan.child(0);
   const int32_t* ch1 = plan.child(1);
@@ -282,6 +283,15 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
               for (int v = 0; v < V; ++v) out[v] = (slot ? o1[v] : o0[v]) == t ? tot[v] : 0.f;
               st_f_stream<V>(dst + t * stride, out);
             }
+          }
+        }
+        // compact form: one value per (leaf, site) = the mass on the leaf's row (its observed-state entry)
+        if (dleaf_obs && active) {
+#pragma unroll
+          for (int slot = 0; slot < 2; ++slot) {
+            const int c = slot ? cc1 : cc0;
+            if ((slot ? gen1 : gen0) || c < 0) continue;
+            st_f_stream<V>(dleaf_obs + (size_t)c * stride, tot);
           }
         }
       } else if (ph < 3) {

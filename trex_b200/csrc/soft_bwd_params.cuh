@@ -18,6 +18,7 @@ struct SoftBwdParams {
   const float* gscale;
   float* gbar;
   float* dleaf;
+  float* dleaf_obs;  // compact leaf gradient [tree][leaf][site] (leaves given as states) or nullptr
   double* dcost;
   int only_direct;  // 1: return immediately when the exp-domain (warp-autonomous) kernel applies
   int phase;        // node list of this launch (common.cuh: Walk): 0 whole tree, 1 segment blockIdx.z, 2 top part

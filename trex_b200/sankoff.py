@@ -97,6 +97,10 @@ class SankoffEngine:
     return self.buf("dleaf", (self.batch, self.n_leaves, self.A, self.stride), torch.float32, zero=True)
 
   @property
+  def dleaf_obs(self):
+    return self.buf("dleaf_obs", (self.batch, self.n_leaves, self.stride), torch.float32, zero=True)
+
+  @property
   def dcost(self):
     return self.buf("dcost", (self.batch, self.A, self.A), torch.float64)
 
@@ -105,7 +109,7 @@ class SankoffEngine:
     return self.buf("edge_hist", (self.batch, self.A, self.A), torch.int64)
 
   # -- site blocks ----------------------------------------------------------------------------
-  _SITE_TABLES = ("leaf", "dp", "argmin", "anc", "root_min", "soft_dp", "gbar", "dleaf")
+  _SITE_TABLES = ("leaf", "dp", "argmin", "anc", "root_min", "soft_dp", "gbar", "dleaf", "dleaf_obs")
 
   def site_block(self, lo: int, hi: int):
     """An engine over sites [lo, hi) of this one's tables (views, no copies; ``lo`` a multiple of 64).
@@ -180,7 +184,17 @@ class SankoffEngine:
 
   def soft_backward(self, cost, temperature, leaf_cost=None, gscale=None, want_dleaf=True,
                     want_dcost=True):
+    """``want_dleaf``: True = dense ``dleaf`` [leaf][A][site]; "compact" = ``dleaf_obs`` [leaf][site]
+    (leaves given as state codes only: the entry at the observed state, every other one is exactly 0)."""
     cost = cost.to(device=self.device, dtype=torch.float32).contiguous()
+    if want_dleaf == "compact":
+      if leaf_cost is not None:
+        raise ValueError("the compact leaf gradient is defined for leaves given as state codes")
+      call("trex_sankoff_soft_bwd_compact", ptr(self.plan), self.n_all, self.n_leaves, self.A, self.L,
+           self.stride, self.batch, ptr(self.leaf), ptr(cost), float(temperature), ptr(self.soft_dp),
+           ptr(gscale), ptr(self.gbar), ptr(self.dleaf_obs), ptr(self.dcost) if want_dcost else None,
+           stream_ptr())
+      return self.gbar
     call("trex_sankoff_soft_bwd", ptr(self.plan), self.n_all, self.n_leaves, self.A, self.L,
          self.stride, self.batch, None if leaf_cost is not None else ptr(self.leaf),
          ptr(leaf_cost), ptr(cost), float(temperature), ptr(self.soft_dp), ptr(gscale),
