@@ -46,6 +46,9 @@ class SankoffEngine:
 
   # -- buffers ------------------------------------------------------------------------------
   def buf(self, name, shape, dtype, zero=False):
+    parent = getattr(self, "_parent", None)
+    if parent is not None and name not in self._own:
+      return parent.buf(name, shape, dtype, zero)
     t = self._bufs.get(name)
     if t is None:
       t = (torch.zeros if zero else torch.empty)(shape, dtype=dtype, device=self.device)
@@ -128,6 +131,14 @@ class SankoffEngine:
       t = getattr(self, name)
       blk._bufs[name] = t[..., lo:, :] if name == "argmin" else t[..., lo:]
     return blk
+
+  def twin(self, own=("leaf", "anc")):
+    """A second engine of the same shape that owns only the tables named in ``own`` and shares every other
+    one (and the plan) with this engine — the second buffer slot of a double-buffered pipeline."""
+    t = SankoffEngine.__new__(SankoffEngine)
+    t.__dict__.update({k: v for k, v in self.__dict__.items() if k != "_bufs"})
+    t._bufs, t._parent, t._own, t._pad_owner = {}, self, set(own), True
+    return t
 
   def site_blocks(self, n_blocks: int):
     per = max(64, ((self.L + n_blocks - 1) // n_blocks + 63) // 64 * 64)
