@@ -68,6 +68,11 @@ TREX_API unsigned long long trex_kernel_launches(void);
 TREX_API size_t trex_sankoff_plan_words(int n_all, int n_leaves);
 TREX_API int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
                       int zero_root_selfloop, int32_t* plan, void* stream);
+/* Same plan, with the number of subtree segments tuned to the alignment the walks will run on (few sites per
+ * GPU -> fewer, larger segments and a shorter serial top part; n_sites <= 0 = unknown = trex_sankoff_plan).
+ * Any plan is valid for any n_sites: the hint only moves time.  Replaces the same reference lines. */
+TREX_API int trex_sankoff_plan_for_sites(const float* adj, int n_all, int n_leaves, int batch,
+                                int zero_root_selfloop, int64_t n_sites, int32_t* plan, void* stream);
 
 /* ---- leaf encoding ------------------------------------------------------------------------
  * `sequences[i].astype(int32)` + scatter index rules of src/trex/sankoff.py:49-52 (negative

@@ -26,6 +26,7 @@ SIGNATURES = {
   "trex_kernel_launches": (C.c_ulonglong, []),
   "trex_sankoff_plan_words": (C.c_size_t, [_i, _i]),
   "trex_sankoff_plan": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+  "trex_sankoff_plan_for_sites": (_i, [_vp, _i, _i, _i, _i, _i64, _vp, _vp]),
   "trex_encode_leaf_states": (_i, [_vp, _i, _i64, _i64, _i, _vp, _i64, _vp]),
   "trex_sankoff_hard_fwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
   "trex_sankoff_traceback": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp]),

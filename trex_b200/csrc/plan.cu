@@ -332,8 +332,30 @@ size_t trex_sankoff_plan_words(int n_all, int n_leaves) {
   return (size_t)trex::kPlanHdr + 9 * (size_t)n_int + 2 * (size_t)trex::kMaxSeg;  // (+ n_int words of builder scratch)
 }
 
-int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
-                      int zero_root_selfloop, int32_t* plan, void* stream) {
+// Segment count the walk kernels get the most out of (measured on B200 in round 2 with tools/probe_seg.py, 1024
+// taxa, A = 20, ms per step = hard fwd + traceback + relaxed fwd + bwd):
+//   12.5k sites: 4 segments 3.07, 8: 1.99, 16: 2.03, 32: 2.19, 64: 2.60      25k: 3.79 3.69 3.67 3.81 4.14
+//   50k sites:   7.18 7.01 6.95 7.07 7.39                                     100k: 13.40 13.17 13.15 13.28 13.63
+// i.e. 16 everywhere except on short alignments, where fewer, larger subtrees shorten the serial top part.
+static int segment_target(long long n_sites, int batch) {
+  int target = 16;
+  if (n_sites > 0) {
+    const double warps = (double)((n_sites + 63) / 64) * (double)batch;  // warps of sites per walk launch
+    if (warps <= 400.0) {
+      const double ideal = (double)trex::sm_count() * 11.0 / warps;  // subtrees side by side that fill the GPU once
+      target = 8;
+      while (target * 1.5 < ideal && target < 64) target *= 2;
+    }
+  }
+  if (const char* e = getenv("TREX_SEG_TARGET")) {  // experiments / tests
+    const int v = atoi(e);
+    if (v >= 1 && v <= trex::kMaxSeg) target = v;
+  }
+  return target;
+}
+
+int trex_sankoff_plan_for_sites(const float* adj, int n_all, int n_leaves, int batch, int zero_root_selfloop,
+                                int64_t n_sites, int32_t* plan, void* stream) {
   using namespace trex;
   TREX_CHECK_ARG(adj && plan, "trex_sankoff_plan: null pointer");
   TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves, "trex_sankoff_plan: need n_all > n_leaves >= 1 (got %d, %d)", n_all, n_leaves);
@@ -353,10 +375,16 @@ int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
                         "cudaFuncSetAttribute(plan_order_kernel)");
     if (rc) return rc;
   }
-  plan_order_kernel<<<batch, kPlanThreads, smem, s>>>(n_all, n_leaves, plan, words, use_smem, kSegTarget);
+  plan_order_kernel<<<batch, kPlanThreads, smem, s>>>(n_all, n_leaves, plan, words, use_smem,
+                                                     segment_target((long long)n_sites, batch));
   note_launches(1);
   TREX_CHECK_LAUNCH("plan_order_kernel");
   return TREX_OK;
+}
+
+int trex_sankoff_plan(const float* adj, int n_all, int n_leaves, int batch,
+                      int zero_root_selfloop, int32_t* plan, void* stream) {
+  return trex_sankoff_plan_for_sites(adj, n_all, n_leaves, batch, zero_root_selfloop, 0, plan, stream);
 }
 
 }  // extern "C"

@@ -151,6 +151,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
   const int tree = blockIdx.y;
   const int n_int = p.n_all - p.n_leaves;
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+  if (p.phase == 1 && (int)blockIdx.z >= plan.hdr()[2]) return;  // empty segment slice: skip the prologue (CTA-uniform)
   {
     float a_uni;
     if (hard_uniform_applies(p, a_uni)) return;  // hard_fwd_uniform_kernel (sankoff_uniform.cu) owns this call
@@ -192,11 +193,22 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
     float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
     uint8_t* arg = p.arg ? p.arg + ((size_t)tree * n_int * A * p.stride + site0) * 2 : nullptr;
     const uint8_t* leaf = p.leaf + site0;
-    const int32_t* order = plan.order();
+    const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+    const int32_t* order = wk.ord;
     const int32_t* ch0 = plan.child(0);
     const int32_t* ch1 = plan.child(1);
     bool bad = false;  // an out-of-range leaf state puts ~1e5 values into internal rows
-    for (int i = 0; i < n_int; ++i) {
+    if (p.phase == 2 && fast_ok) {
+      // the top part consumes rows of the subtree segments (another launch): a stateless leaf anywhere below
+      // disables the packed-key path exactly as in the single walk, so look at all leaves of these sites
+      for (int c = 0; c < p.n_leaves; ++c) {
+        int o[V];
+        ld_u8<V>(leaf + (size_t)c * p.stride, o);
+#pragma unroll
+        for (int v = 0; v < V; ++v) bad = bad || o[v] >= A;
+      }
+    }
+    for (int i = 0; i < wk.n_fwd; ++i) {
       const int node = __ldg(order + i);
       const int k = node - p.n_leaves;
       const int c0 = __ldg(ch0 + k), c1 = __ldg(ch1 + k);
@@ -232,9 +244,9 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
       }
 #undef TREX_NODE
     }
-    if (p.root_min) st_f<V>(p.root_min + (size_t)tree * p.stride + site0, rmin);
+    if (p.root_min && p.phase != 1) st_f<V>(p.root_min + (size_t)tree * p.stride + site0, rmin);
   }
-  if (p.total) {
+  if (p.total && p.phase != 1) {
     double acc = 0.0;
     if (active) {
 #pragma unroll
@@ -249,9 +261,18 @@ template <int AP, int V>
 static int launch_hard(const HardFwdParams& p, int batch, cudaStream_t s) {
   constexpr int THREADS = 128;
   const long long nvec = (p.n_sites + V - 1) / V;
-  dim3 grid((unsigned)((nvec + THREADS - 1) / THREADS), batch);
-  hard_fwd_kernel<AP, V, THREADS><<<grid, THREADS, 0, s>>>(p);
-  note_launches(1);
+  const unsigned gx = (unsigned)((nvec + THREADS - 1) / THREADS);
+  if (use_segments(p.n_leaves)) {
+    HardFwdParams q = p;
+    q.phase = 1;  // independent subtrees side by side ...
+    hard_fwd_kernel<AP, V, THREADS><<<dim3(gx, batch, kMaxSeg), THREADS, 0, s>>>(q);
+    q.phase = 2;  // ... then the nodes above them
+    hard_fwd_kernel<AP, V, THREADS><<<dim3(gx, batch), THREADS, 0, s>>>(q);
+    note_launches(2);
+  } else {
+    hard_fwd_kernel<AP, V, THREADS><<<dim3(gx, batch), THREADS, 0, s>>>(p);
+    note_launches(1);
+  }
   return check_cuda(cudaPeekAtLastError(), "hard_fwd_kernel");
 }
 

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
   const float c1 = 1.4426950408889634f / p.T;
 
+  if (p.phase == 1 && (int)blockIdx.z >= plan.hdr()[2]) return;  // empty segment slice: skip the prologue (CTA-uniform)
   {
     float a_uni;
     if (soft_bwd_uniform_applies(p, a_uni)) return;  // soft_bwd_uniform_kernel owns this call
@@ -135,10 +136,13 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   float* gbar = p.gbar + (size_t)tree * n_int * A * stride + site0;
   float* dleaf = p.dleaf ? p.dleaf + (size_t)tree * p.n_leaves * A * stride + site0 : nullptr;
   float* dleaf_obs = p.dleaf_obs ? p.dleaf_obs + (size_t)tree * p.n_leaves * stride + site0 : nullptr;
-  const int32_t* order = plan.order();
+  const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+  const int32_t* order = wk.ord;  // this launch walks order[n_reach-1] down to order[0]
+  const int n_reach = wk.n_rev;
+  if (n_reach == 0) return;
+  const bool has_root = __ldg(order + n_reach - 1) == p.n_all - 1;  // the root is the last reachable node
   const int32_t* ch0 = plan.child(0);
   const int32_t* ch1 = plan.child(1);
-  const int n_reach = plan.hdr()[1];
   float* myR = sR + lane * V;  // this lane's column of the staged rows
   float* myE = sE + lane * V;
 
@@ -159,13 +163,13 @@ __global__ void __launch_bounds__(32 * W, (AP > 8 ? 11 : 16) / W) soft_bwd_warp_
   }
 
   // ---- nodes the root does not reach get zero cotangent; root: gscale * softmax(-dp/T) --------
-  {
+  if (has_root) {  // (the walk that owns the root)
     float zero[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) zero[v] = 0.f;
     if (active) {
-      for (int i = n_reach; i < n_int; ++i) {
-        float* row = gbar + (size_t)(__ldg(order + i) - p.n_leaves) * A * stride;
+      for (int i = plan.hdr()[1]; i < n_int; ++i) {
+        float* row = gbar + (size_t)(__ldg(plan.order() + i) - p.n_leaves) * A * stride;
         for (int s = 0; s < A; ++s) st_f<V>(row + s * stride, zero);
       }
     }
@@ -493,21 +497,26 @@ static int launch_warp(const SoftBwdParams& p, int batch, cudaStream_t s) {
   using Cfg = WarpCfg<AP, V>;
   const size_t smem = sizeof(float) * (Cfg::kSharedFloats + (size_t)W * Cfg::kWarpFloats);
   const long long nwarps = (p.n_sites + Cfg::NS - 1) / Cfg::NS;
-  dim3 grid((unsigned)((nwarps + W - 1) / W), batch);
-  cudaError_t e;
-  if (p.dcost) {
-    auto kern = soft_bwd_warp_kernel<AP, V, W, true>;
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd_warp)");
-    kern<<<grid, 32 * W, smem, s>>>(p);
-    note_launches(1);
-  } else {
-    auto kern = soft_bwd_warp_kernel<AP, V, W, false>;
-    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd_warp)");
-    kern<<<grid, 32 * W, smem, s>>>(p);
-    note_launches(1);
-  }
+  const unsigned gx = (unsigned)((nwarps + W - 1) / W);
+  const bool segs = use_segments(p.n_leaves);
+  auto go = [&](auto kern) -> cudaError_t {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    SoftBwdParams q = p;
+    if (segs) {
+      q.phase = 2;  // the nodes above the segments first (root downwards) ...
+      kern<<<dim3(gx, batch), 32 * W, smem, s>>>(q);
+      q.phase = 1;  // ... then the independent subtrees side by side
+      kern<<<dim3(gx, batch, kMaxSeg), 32 * W, smem, s>>>(q);
+      note_launches(2);
+    } else {
+      kern<<<dim3(gx, batch), 32 * W, smem, s>>>(q);
+      note_launches(1);
+    }
+    return e;
+  };
+  const cudaError_t e = p.dcost ? go(soft_bwd_warp_kernel<AP, V, W, true>) : go(soft_bwd_warp_kernel<AP, V, W, false>);
+  if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd_warp)");
   return check_cuda(cudaPeekAtLastError(), "soft_bwd_warp_kernel");
 }
 

@@ -130,6 +130,7 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
   const float c1 = 1.4426950408889634f / p.T;   // log2(e)/T
   const float tln2 = p.T * 0.6931471805599453f;  // T*ln(2)
+  if (p.phase == 1 && (int)blockIdx.z >= plan.hdr()[2]) return;  // empty segment slice: skip the prologue (CTA-uniform)
   {
     float a_uni;
     if (soft_uniform_applies(p, a_uni)) return;  // soft_fwd_uniform_kernel (sankoff_uniform.cu) owns this call
@@ -163,13 +164,15 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p
 
   const long long site0 = ((long long)blockIdx.x * THREADS + tid) * V;
   const bool active = site0 < p.n_sites;
+  const Walk wk = make_walk(plan, p.phase, blockIdx.z);
+  const bool has_root = p.phase != 1;  // the whole-tree walk and the top part end at the root
   double acc = 0.0;
   if (active) {
     float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
-    const int32_t* order = plan.order();
+    const int32_t* order = wk.ord;
     const int32_t* ch0 = plan.child(0);
     const int32_t* ch1 = plan.child(1);
-    for (int i = 0; i < n_int; ++i) {
+    for (int i = 0; i < wk.n_fwd; ++i) {
       const int node = __ldg(order + i);
       const int k = node - p.n_leaves;
       const int c0 = __ldg(ch0 + k), c1n = __ldg(ch1 + k);
@@ -213,6 +216,7 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p
 #undef TREX_SNODE
     }
     // total += softmin_s dp[root][s]   (sankoff.py:187 relaxed)
+    if (has_root) {
     float x[AP][V];
     load_row<AP, V>(dp + (size_t)(n_int - 1) * A * p.stride, A, p.stride, x);
 #pragma unroll
@@ -225,17 +229,27 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p
       for (int s = 0; s < AP; ++s) z += exp2f((mm - x[s][v]) * c1);
       if (site0 + v < p.n_sites) acc += (double)fmaf(-tln2, __log2f(z), mm);
     }
+    }
   }
-  if (p.total) block_atomic_add(acc, p.total + tree);
+  if (p.total && has_root) block_atomic_add(acc, p.total + tree);
 }
 
 template <int AP, int V>
 static int launch_soft_fwd(const SoftFwdParams& p, int batch, cudaStream_t s) {
   constexpr int THREADS = 128;
   const long long nvec = (p.n_sites + V - 1) / V;
-  dim3 grid((unsigned)((nvec + THREADS - 1) / THREADS), batch);
-  soft_fwd_kernel<AP, V, THREADS><<<grid, THREADS, 0, s>>>(p);
-  note_launches(1);
+  const unsigned gx = (unsigned)((nvec + THREADS - 1) / THREADS);
+  if (use_segments(p.n_leaves)) {
+    SoftFwdParams q = p;
+    q.phase = 1;  // independent subtrees side by side ...
+    soft_fwd_kernel<AP, V, THREADS><<<dim3(gx, batch, kMaxSeg), THREADS, 0, s>>>(q);
+    q.phase = 2;  // ... then the nodes above them
+    soft_fwd_kernel<AP, V, THREADS><<<dim3(gx, batch), THREADS, 0, s>>>(q);
+    note_launches(2);
+  } else {
+    soft_fwd_kernel<AP, V, THREADS><<<dim3(gx, batch), THREADS, 0, s>>>(p);
+    note_launches(1);
+  }
   return check_cuda(cudaPeekAtLastError(), "soft_fwd_kernel");
 }
 

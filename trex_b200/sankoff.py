@@ -152,8 +152,8 @@ class SankoffEngine:
     if adj.dim() == 2:
       adj = adj.unsqueeze(0).expand(self.batch, -1, -1).contiguous() if self.batch > 1 else adj.unsqueeze(0)
     assert adj.shape == (self.batch, self.n_all, self.n_all), adj.shape
-    call("trex_sankoff_plan", ptr(adj), self.n_all, self.n_leaves, self.batch,
-         1 if zero_root_selfloop else 0, ptr(self.plan), stream_ptr())
+    call("trex_sankoff_plan_for_sites", ptr(adj), self.n_all, self.n_leaves, self.batch,
+         1 if zero_root_selfloop else 0, self.L, ptr(self.plan), stream_ptr())
     return self
 
   def set_leaf_states_u8(self, states):
