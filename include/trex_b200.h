@@ -205,6 +205,26 @@ TREX_API int trex_compute_cost(const float* seqs_one_hot, const float* adjacency
                       int n_nodes, int64_t n_sites, int n_states, int32_t* state_scratch,
                       int32_t* parent_scratch, double* acc_scratch, float* out_cost, void* stream);
 
+/* ---- allocation-free variant of trex_compute_cost --------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * trex_compute_cost, but the three scratch buffers (state [N][L] i32, parent [N] i32, one f64 accumulator) live
+ * in a static device array inside the library instead of being passed in: 256 + 4 * TREX_NOALLOC_MAX_NODES +
+ * 4 * TREX_NOALLOC_MAX_CELLS bytes (= 4 MiB + 16.25 KiB), resident on every GPU that loads the library until
+ * the process exits.  The call makes no cudaMalloc / cudaFree and calls no allocating library routine; the caller
+ * still passes inputs and the output.
+ *   Limits: n_nodes <= TREX_NOALLOC_MAX_NODES and n_nodes * n_sites <= TREX_NOALLOC_MAX_CELLS; anything larger is
+ *   rejected with TREX_ERR_INVALID_ARGUMENT (trex_last_error names the limit) before any CUDA call is made.
+ *   Sharing: every call on a device uses the SAME array, which keeps the previous call's contents (the
+ *   accumulator is cleared by each call, the two tables are fully overwritten).  Calls that overlap on one GPU
+ *   (different streams, or concurrently replayed graphs) RACE on it: serialise them, or use trex_compute_cost with
+ *   per-call scratch. */
+#define TREX_NOALLOC_MAX_NODES 4096
+#define TREX_NOALLOC_MAX_CELLS (1LL << 20)
+TREX_API size_t trex_compute_cost_noalloc_scratch_bytes(void);
+TREX_API int trex_compute_cost_noalloc(const float* seqs_one_hot, const float* adjacency, const float* subst,
+                              int n_nodes, int64_t n_sites, int n_states, float* out_cost, void* stream);
+
 /* ---- whole ancestor-fitting loop on the device ------------------------------
  * Replaces the body of run_trex_optimization_configurable (src/trex/evals/benchmark.py:75-200):
  * n_iterations of { loss, grads = value_and_grad(loss_fn)(ancestors); optimizer.update; apply_updates }

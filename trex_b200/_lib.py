@@ -46,6 +46,8 @@ SIGNATURES = {
   "trex_graph_constraint": (_i, [_vp, _i, _f, _vp, _vp, _vp, _vp]),
   "trex_discretize_topology": (_i, [_vp, _i, _vp, _vp, _vp]),
   "trex_compute_cost": (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp, _vp, _vp, _vp]),
+  "trex_compute_cost_noalloc_scratch_bytes": (C.c_size_t, []),
+  "trex_compute_cost_noalloc": (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp]),
   "trex_landscape_loss_fwd_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
   "trex_fit_ancestors_workspace_bytes": (C.c_size_t, [_i, _i, _i64, _i]),
   "trex_fit_ancestors": (_i, [_vp, _vp, _i, _i, _i64, _i, _vp, _vp, _vp, _i, _f, _f, _i, _i64, _vp, _vp, _vp, _vp]),

@@ -282,4 +282,98 @@ int trex_compute_cost(const float* seqs_one_hot, const float* adjacency, const f
   return TREX_OK;
 }
 
+
+// ---- no-allocation variant of trex_compute_cost -------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The three scratch
+// buffers of trex_compute_cost live in ONE file-scope device array of a fixed, modest size, resident on every
+// GPU that loads the library until the process exits:
+//   [0, 256)                      f64 accumulator (must start at zero: cleared by every call)
+//   [256, 256 + 4 * kNaMaxNodes)  i32 parent[n_nodes]   (fully overwritten by every call)
+//   [.., + 4 * kNaMaxCells)       i32 state[n_nodes][n_sites] (fully overwritten by every call)
+// In host code the array's name is only a host-side stand-in for the symbol, not a device address: the address
+// is looked up once per device with cudaGetSymbolAddress (that device current) and cached.
+}  // extern "C" (closed for the file-scope definitions below)
+
+#include <mutex>
+
+namespace {
+constexpr int kNaMaxNodes = TREX_NOALLOC_MAX_NODES;
+constexpr long long kNaMaxCells = TREX_NOALLOC_MAX_CELLS;
+constexpr size_t kNaParentOff = 256;
+constexpr size_t kNaStateOff = kNaParentOff + sizeof(int32_t) * (size_t)kNaMaxNodes;
+constexpr size_t kNaBytes = kNaStateOff + sizeof(int32_t) * (size_t)kNaMaxCells;
+static_assert(kNaStateOff % 256 == 0, "state table must stay 256-byte aligned");
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+namespace {
+std::mutex g_na_mutex;
+unsigned char* g_na_ptr[64] = {nullptr};  // device address of g_noalloc_scratch, per device ordinal
+
+// device address of the scratch array on the CURRENT device (looked up once per device); nullptr + error set on failure
+unsigned char* noalloc_scratch_ptr() {
+  int dev = -1;
+  if (trex::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return nullptr;
+  if (dev < 0 || dev >= 64) {
+    trex::set_error("trex_compute_cost_noalloc: device ordinal %d out of range", dev);
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_na_mutex);
+  if (!g_na_ptr[dev]) {
+    void* p = nullptr;
+    if (trex::check_cuda(cudaGetSymbolAddress(&p, g_noalloc_scratch), "cudaGetSymbolAddress(g_noalloc_scratch)"))
+      return nullptr;
+    g_na_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  return g_na_ptr[dev];
+}
+}  // namespace
+
+extern "C" {
+
+size_t trex_compute_cost_noalloc_scratch_bytes(void) { return kNaBytes; }
+
+int trex_compute_cost_noalloc(const float* seqs_one_hot, const float* adjacency, const float* subst, int n_nodes,
+                              int64_t n_sites, int n_states, float* out_cost, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(seqs_one_hot && adjacency && subst && out_cost, "trex_compute_cost_noalloc: null pointer");
+  TREX_CHECK_ARG(n_nodes >= 1 && n_sites >= 1 && n_states >= 1, "trex_compute_cost_noalloc: bad sizes");
+  // size limits first: nothing below runs, and no CUDA call is made, for a problem the static scratch cannot hold
+  TREX_CHECK_ARG(n_nodes <= kNaMaxNodes,
+                 "trex_compute_cost_noalloc: n_nodes %d exceeds the static scratch limit TREX_NOALLOC_MAX_NODES = %d "
+                 "(use trex_compute_cost with caller-provided scratch)", n_nodes, kNaMaxNodes);
+  TREX_CHECK_ARG((long long)n_nodes * (long long)n_sites <= kNaMaxCells,
+                 "trex_compute_cost_noalloc: n_nodes * n_sites = %lld exceeds the static scratch limit "
+                 "TREX_NOALLOC_MAX_CELLS = %lld (use trex_compute_cost with caller-provided scratch)",
+                 (long long)n_nodes * (long long)n_sites, kNaMaxCells);
+  unsigned char* base = noalloc_scratch_ptr();
+  if (!base) return TREX_ERR_CUDA;
+  double* acc = reinterpret_cast<double*>(base);
+  int32_t* parent = reinterpret_cast<int32_t*>(base + kNaParentOff);
+  int32_t* state = reinterpret_cast<int32_t*>(base + kNaStateOff);
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long rows = (long long)n_nodes * n_sites;
+  // the array keeps the previous call's contents: the accumulator is the one part that must start at zero
+  int rc = check_cuda(cudaMemsetAsync(acc, 0, sizeof(double), s), "memset");
+  if (rc) return rc;
+  row_argmax_kernel<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(seqs_one_hot, rows, n_states, state);
+  note_launches(1);
+  TREX_CHECK_LAUNCH("row_argmax_kernel");
+  row_argmax_kernel<<<(n_nodes + 127) / 128, 128, 0, s>>>(adjacency, n_nodes, n_nodes, parent);
+  note_launches(1);
+  TREX_CHECK_LAUNCH("row_argmax_kernel");
+  if (n_nodes > 1) {
+    dim3 grid((unsigned)((n_sites + 255) / 256), n_nodes - 1);  // [:-1] drops the last node
+    compute_cost_kernel<<<grid, 256, 0, s>>>(state, parent, subst, n_nodes, n_sites, n_states, acc);
+    note_launches(1);
+    TREX_CHECK_LAUNCH("compute_cost_kernel");
+  }
+  finish_scalar_kernel<<<1, 1, 0, s>>>(acc, out_cost);
+  note_launches(1);
+  TREX_CHECK_LAUNCH("finish_scalar_kernel");
+  return TREX_OK;
+}
+
 }  // extern "C"
