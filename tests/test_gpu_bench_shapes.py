@@ -179,3 +179,33 @@ def test_relaxed_path_vs_float64_oracle_at_bench_shapes(shape, cost_kind, T, seg
     picked = np.take_along_axis(g64[:, :n], states.T[:, :, None].astype(np.int64), axis=2)[:, :, 0].T
     assert np.abs(want_obs - picked).max() <= 1e-12                        # ... which is the observed-state entry
     assert np.abs(obs - want_obs).max() <= RTOL
+
+
+@pytest.mark.parametrize("T", [1.0, 0.1])
+def test_wide_reverse_kernel_build_vs_float64_oracle(T):
+  """The 255-register build of the uniform-cost reverse kernel (sankoff_soft_bwd_uniform.cu: WIDE) is what the
+  bench runs at 100k sites; the launcher picks it from ~76k sites on, so it is forced here on the c5 slice."""
+  shape, cost_kind = "c5slice", "unit"
+  n, A, L, _ = SHAPES[shape]
+  tot64, dC64, dp64, g64 = _soft_oracle(shape, cost_kind, T)
+  old = os.environ.get("TREX_BWD_WIDE")
+  os.environ["TREX_BWD_WIDE"] = "1"
+  try:
+    eng, cost = _engine(shape, cost_kind)
+    eng.soft_forward(cost, T)
+    gtol = max(RTOL, 2.0 ** -24 * np.abs(dp64[:, n:]).max() / T)
+    for mode in (True, "compact"):
+      eng.gbar.zero_()
+      eng.soft_backward(cost, T, want_dleaf=mode, want_dcost=True)
+      gbar = eng.gbar[0, :, :, :L].permute(2, 0, 1).cpu().numpy()
+      assert np.abs(gbar - g64[:, n:]).max() <= gtol
+      assert np.abs(eng.dcost[0].cpu().numpy() - dC64).max() <= RTOL * np.abs(dC64).max()
+    dleaf = eng.dleaf[0, :, :, :L].permute(2, 0, 1).cpu().numpy()
+    assert np.abs(dleaf - g64[:, :n]).max() <= RTOL
+    obs = eng.dleaf_obs[0, :, :L].cpu().numpy()
+    assert np.abs(obs - g64[:, :n].sum(axis=2).T).max() <= RTOL
+  finally:
+    if old is None:
+      os.environ.pop("TREX_BWD_WIDE", None)
+    else:
+      os.environ["TREX_BWD_WIDE"] = old

@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtrex_b200.so")
+# TREX_B200_LIB: load another build of the same library (kernel-variant experiments); default = the in-tree build
+LIB_PATH = os.environ.get("TREX_B200_LIB") or os.path.join(_HERE, "libtrex_b200.so")
 
 MODE_AUTO = 0
 MODE_GENERAL = 1

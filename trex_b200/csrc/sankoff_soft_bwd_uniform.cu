@@ -18,6 +18,8 @@
 // The dC outer product is the pair-tile sweep of the warp kernel: lane = (pair tile, site group),
 // TR x TC grid of RS x CS register tiles, 128-bit conflict-free shared loads, f32 partial sums
 // flushed every kFlush nodes into a warp-private f64 table, f64 atomics once at the end.
+#include <cstdlib>
+
 #include "fwd_params.cuh"
 #include "soft_bwd_params.cuh"
 
@@ -62,12 +64,12 @@ __device__ __forceinline__ void cp_async_v(float* smem_dst, const float* gsrc, i
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // acc[a][b] += sum over this lane's site group of r[a][site] * e[b][site]
-template <int AP, int V>
+template <int AP, int V, int UNROLL>
 __device__ __forceinline__ void pair_sweep(const float* __restrict__ rbase, const float* __restrict__ ebase,
                                            float (&acc)[UniCfg<AP, V>::RS][UniCfg<AP, V>::CS]) {
   using Cfg = UniCfg<AP, V>;
   constexpr int RS = Cfg::RS, CS = Cfg::CS, PITCH = Cfg::PITCH, SG = Cfg::SG;
-#pragma unroll 1
+#pragma unroll(UNROLL)
   for (int it = 0; it < Cfg::NCH; ++it) {
     float4 rr[RS], ee[CS];
 #pragma unroll
@@ -91,9 +93,18 @@ __device__ __forceinline__ void pair_sweep(const float* __restrict__ rbase, cons
 }  // namespace
 
 // FULL: n_states == AP (no padded state rows, no per-row guards)
-template <int AP, int V, bool WANT_DC, bool FULL>
-__global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(const SoftBwdParams p) {
+// WIDE: the long-alignment build of the dC kernel.  Registers are allocated per SM sub-partition (16 384 each), so
+// with 9-12 one-warp CTAs per SM some sub-partition hosts three warps and ptxas caps the kernel at 168 registers —
+// where this kernel spills and the dC sweep cannot be unrolled (every one of its 8 iterations then exposes a full
+// LDS latency: 17 % of the stall samples, profiles/r02_g_soft_bwd_uniform_hot_lines.txt).  At 8 CTAs per SM the cap
+// is 255: no spills and a 4x unrolled sweep whose loads run ahead of the FMAs.  Measured at 1024 taxa x 100k sites,
+// A = 20 (profiles/r02_h_soft_bwd_variants.txt): 8.30 -> 7.69 ms; at 12.5k sites (too few warps to fill the GPU
+// either way) 1.17 -> 1.37 ms, and without dC 5.11 -> 5.56 ms, so the launcher picks WIDE only for dC on long
+// alignments.
+template <int AP, int V, bool WANT_DC, bool FULL, bool WIDE = false>
+__global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_uniform_kernel(const SoftBwdParams p) {
   using Cfg = UniCfg<AP, V>;
+  constexpr int kSweepUnroll = WIDE ? 4 : 1;
   constexpr int RS = Cfg::RS, CS = Cfg::CS, NT = Cfg::NT, PITCH = Cfg::PITCH;
   float a_off;
   if (!soft_bwd_uniform_applies(p, a_off)) return;  // the general kernels own every other cost matrix
@@ -294,7 +305,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
     }
     if (WANT_DC) {
       __syncwarp();
-      pair_sweep<AP, V>(rbase, ebase, acc);
+      pair_sweep<AP, V, kSweepUnroll>(rbase, ebase, acc);
       __syncwarp();
     }
   };
@@ -419,7 +430,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
       }
       if (WANT_DC) {
         __syncwarp();
-        pair_sweep<AP, V>(gbase, ebase, accG);
+        pair_sweep<AP, V, kSweepUnroll>(gbase, ebase, accG);
         __syncwarp();
       }
       // rare: lanes whose child has no state (missing child, state out of range): all-1e5 child row,
@@ -469,7 +480,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? 11 : 16) soft_bwd_uniform_kernel(
         }
         if (WANT_DC) {
           __syncwarp();
-          pair_sweep<AP, V>(rbase, ebase, acc);
+          pair_sweep<AP, V, kSweepUnroll>(rbase, ebase, acc);
           __syncwarp();
         }
       }
@@ -523,8 +534,14 @@ int launch_uniform(const SoftBwdParams& p0, int batch, cudaStream_t s) {
   };
   const SoftBwdParams& p = p0;
   const bool full = p.n_states == AP;
+  // long alignments (at least 4 warps of sites per SM): the 255-register build of the dC kernel
+  bool wide = AP > 8 && full && (long long)gx * batch >= 4LL * sm_count();  // measured: wins from 50k sites up, loses at 12.5k
+  if (const char* e = getenv("TREX_BWD_WIDE")) {  // tests: force the choice (the builds are parity-tested against each other's oracle)
+    if (e[0] == '0' || e[0] == '1') wide = AP > 8 && full && e[0] == '1';
+  }
   cudaError_t e;
-  if (p.dcost) e = full ? go(soft_bwd_uniform_kernel<AP, V, true, true>) : go(soft_bwd_uniform_kernel<AP, V, true, false>);
+  if (p.dcost && wide) e = go(soft_bwd_uniform_kernel<AP, V, true, true, true>);
+  else if (p.dcost) e = full ? go(soft_bwd_uniform_kernel<AP, V, true, true>) : go(soft_bwd_uniform_kernel<AP, V, true, false>);
   else e = full ? go(soft_bwd_uniform_kernel<AP, V, false, true>) : go(soft_bwd_uniform_kernel<AP, V, false, false>);
   if (e != cudaSuccess) return check_cuda(e, "cudaFuncSetAttribute(soft_bwd_uniform)");
   return check_cuda(cudaPeekAtLastError(), "soft_bwd_uniform_kernel");
