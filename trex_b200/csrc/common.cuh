@@ -151,6 +151,20 @@ __device__ __forceinline__ void ld_u8(const uint8_t* __restrict__ p, int (&out)[
   }
 }
 
+// The V state bytes of a lane as ONE raw word, unpacked later: a prefetch that is consumed a node ahead must not
+// convert the bytes at the load (the conversion would wait for the load right there).
+template <int V>
+__device__ __forceinline__ unsigned ld_u8_raw(const uint8_t* __restrict__ p) {
+  if constexpr (V == 1) return *p;
+  else if constexpr (V == 2) return *reinterpret_cast<const unsigned short*>(p);
+  else return *reinterpret_cast<const unsigned*>(p);
+}
+template <int V>
+__device__ __forceinline__ void unpack_u8(unsigned raw, int (&out)[V]) {
+#pragma unroll
+  for (int v = 0; v < V; ++v) out[v] = (int)((raw >> (8 * v)) & 0xffu);
+}
+
 template <int V>
 __device__ __forceinline__ void st_u8(uint8_t* __restrict__ p, const int (&v)[V]) {
   if constexpr (V == 1) {

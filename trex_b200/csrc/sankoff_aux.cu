@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
   const int tree = blockIdx.y;
   const int n_int = p.n_all - p.n_leaves;
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
+  if (p.phase == 1 && (int)blockIdx.z >= plan.hdr()[2]) return;  // empty segment slice (CTA-uniform)
   if (p.hist) {
     for (int i = threadIdx.x; i < A * A; i += THREADS) s_hist[i] = 0;
     __syncthreads();

@@ -106,6 +106,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
   using Cfg = UniCfg<AP, V>;
   constexpr int kSweepUnroll = WIDE ? 4 : 1;
   constexpr int RS = Cfg::RS, CS = Cfg::CS, NT = Cfg::NT, PITCH = Cfg::PITCH;
+  if (p.phase == 1 && (int)blockIdx.z >= (p.plan + (size_t)blockIdx.y * p.plan_words)[2]) return;  // empty segment slice (CTA-uniform): before any other work
   float a_off;
   if (!soft_bwd_uniform_applies(p, a_off)) return;  // the general kernels own every other cost matrix
   extern __shared__ __align__(16) float smem[];
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
     int k, cA, cB;      // children are taken "forwarded child last"
     bool fwdB;          // cB is the next node of the walk: its gbar row stays in sG as the next cotangent
     const float *srcA, *srcB;
-    int oA[V], oB[V];   // observed states of state children (A: no state, -1: child has a cost row)
+    unsigned rawA, rawB;  // observed-state bytes of state children, still packed (unpacked where they are used)
   };
   auto decode = [&](int j, Desc& q) {
     const int node = __ldg(order + j);
@@ -194,10 +195,9 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
     q.fwdB = q.cB == nq && q.cB >= p.n_leaves;
     q.srcA = row_src(q.cA);
     q.srcB = row_src(q.cB);
-#pragma unroll
-    for (int v = 0; v < V; ++v) { q.oA[v] = q.srcA ? -1 : A; q.oB[v] = q.srcB ? -1 : A; }
-    if (!q.srcA && q.cA >= 0 && p.leaf) ld_u8<V>(p.leaf + (size_t)q.cA * stride + site0, q.oA);
-    if (!q.srcB && q.cB >= 0 && p.leaf) ld_u8<V>(p.leaf + (size_t)q.cB * stride + site0, q.oB);
+    q.rawA = q.rawB = 0xffffffffu;  // "no state" in every byte (missing child / leaf without a state table)
+    if (!q.srcA && q.cA >= 0 && p.leaf) q.rawA = ld_u8_raw<V>(p.leaf + (size_t)q.cA * stride + site0);
+    if (!q.srcB && q.cB >= 0 && p.leaf) q.rawB = ld_u8_raw<V>(p.leaf + (size_t)q.cB * stride + site0);
   };
 
   // ---- nodes the root does not reach get zero cotangent; root: gscale * softmax(-dp/T) --------
@@ -254,6 +254,14 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
       for (int t = 0; t < AP; ++t)
         if (FULL || t < A) ld_f_stream<V>(src + (size_t)t * stride, d[t]);
     }
+    // WIDE: the cotangent rows go to registers up front (all LDS in flight behind the exp math below) and r stays
+    // there; the narrow build has no registers for that and round-trips r through the R slab, where every LDS
+    // waits behind the previous STS (the G and R slabs swap roles, so the compiler cannot reorder them).
+    float gr[WIDE ? AP : 1][V];
+    if constexpr (WIDE) {
+#pragma unroll
+      for (int s = 0; s < AP; ++s) ld_f<V>(myG + s * PITCH, gr[s]);
+    }
     float kE[V], R[V];
 #pragma unroll
     for (int v = 0; v < V; ++v) {
@@ -272,6 +280,28 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
       kE[v] = kk * (E0 + E1);
       R[v] = 0.f;
     }
+    if constexpr (WIDE) {  // (WIDE implies FULL and WANT_DC)
+#pragma unroll
+      for (int s = 0; s < AP; ++s) {
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          gr[s][v] *= rcp_fast(fmaf(km1, d[s][v], kE[v]));  // r[s] = g[s] / Z[s],  Z >= k > 0
+          R[v] += gr[s][v];
+        }
+        st_f<V>(myR + s * PITCH, gr[s]);
+        st_f<V>(myE + s * PITCH, d[s]);
+      }
+#pragma unroll
+      for (int v = 0; v < V; ++v) R[v] *= kk;
+#pragma unroll
+      for (int t = 0; t < AP; ++t) {
+        float r[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) r[v] = d[t][v] * fmaf(km1, gr[t][v], R[v]);  // e[t] ((1-k) r[t] + k R)
+        if (dst && active) st_f<V>(dst + (size_t)t * stride, r);
+        if (forward) st_f<V>(myG + t * PITCH, r);
+      }
+    } else {
 #pragma unroll
     for (int s = 0; s < AP; ++s)
       if (FULL || s < A) {
@@ -297,6 +327,7 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
         if (dst && active) st_f<V>(dst + (size_t)t * stride, r);
         if (forward) st_f<V>(myG + t * PITCH, r);
       }
+    }
     pf_src = next_src;
     if (next_src) {
 #pragma unroll
@@ -378,12 +409,14 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
 
     if (!srcA || !srcB) {
       // ---- children given as states (or missing): one g-space sweep for both -----------------
-      int oA[V], oB[V];
+      int oA[V], oB[V];  // A: no state, -1: the child has a cost row (handled below, not here)
       bool nA = false, nB = false;
+      unpack_u8<V>(cur.rawA, oA);
+      unpack_u8<V>(cur.rawB, oB);
 #pragma unroll
       for (int v = 0; v < V; ++v) {
-        oA[v] = min(cur.oA[v], A);
-        oB[v] = min(cur.oB[v], A);
+        oA[v] = srcA ? -1 : min(oA[v], A);
+        oB[v] = srcB ? -1 : min(oB[v], A);
         nA = nA || (oA[v] == A && ok[v]);
         nB = nB || (oB[v] == A && ok[v]);
       }

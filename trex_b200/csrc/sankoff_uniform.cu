@@ -160,6 +160,7 @@ __device__ __forceinline__ void leaf_first_min(const int (&o)[V], int A, float a
 template <int AP, int V, int THREADS, bool FULL, bool WANT_ARG>
 __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwdParams p) {
   float a;
+  if (p.phase == 1 && (int)blockIdx.z >= (p.plan + (size_t)blockIdx.y * p.plan_words)[2]) return;  // empty segment slice (CTA-uniform): before any other work
   if (!hard_uniform_applies(p, a)) return;
   const int A = FULL ? AP : p.n_states;
   const int tree = blockIdx.y;
@@ -348,6 +349,7 @@ __device__ __forceinline__ void leaf_exp_domain(const int (&o)[V], int A, float 
 template <int AP, int V, int THREADS, bool FULL>
 __global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwdParams p) {
   float a;
+  if (p.phase == 1 && (int)blockIdx.z >= (p.plan + (size_t)blockIdx.y * p.plan_words)[2]) return;  // empty segment slice (CTA-uniform): before any other work
   if (!soft_uniform_applies(p, a)) return;
   const int A = FULL ? AP : p.n_states;
   const int tree = blockIdx.y;
