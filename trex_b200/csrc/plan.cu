@@ -53,7 +53,7 @@ int sm_count() {
 // ---- kernel 1: first two rows with adj[row, col] == 1 for every internal column -----------
 // CTA = 32 columns x 8 row chunks; a warp reads 32 consecutive columns of one row (coalesced).
 constexpr int kColsPerCta = 32;
-constexpr int kRowChunks = 8;
+constexpr int kRowChunks = 32;  // (8: 44 us per 2047-node adjacency, latency-bound on 32 CTAs of 256 threads)
 
 __global__ void __launch_bounds__(kColsPerCta* kRowChunks)
     plan_children_kernel(const float* __restrict__ adj, int n_all, int n_leaves,
@@ -332,21 +332,14 @@ size_t trex_sankoff_plan_words(int n_all, int n_leaves) {
   return (size_t)trex::kPlanHdr + 9 * (size_t)n_int + 2 * (size_t)trex::kMaxSeg;  // (+ n_int words of builder scratch)
 }
 
-// Segment count the walk kernels get the most out of (measured on B200 in round 2 with tools/probe_seg.py, 1024
-// taxa, A = 20, ms per step = hard fwd + traceback + relaxed fwd + bwd):
-//   12.5k sites: 4 segments 3.07, 8: 1.99, 16: 2.03, 32: 2.19, 64: 2.60      25k: 3.79 3.69 3.67 3.81 4.14
-//   50k sites:   7.18 7.01 6.95 7.07 7.39                                     100k: 13.40 13.17 13.15 13.28 13.63
-// i.e. 16 everywhere except on short alignments, where fewer, larger subtrees shorten the serial top part.
+// Segment count the walk kernels get the most out of: measured on B200 in round 2 (tools/probe_step.py, 1024 taxa,
+// A = 20, ms per step = hard fwd + traceback + relaxed fwd + bwd; profiles/r02_j_probe_step.txt):
+//   12.5k sites: 8 segments 2.07, 16: 1.82, 32: 1.93      25k sites: 3.31  3.28  3.33      100k: flat between 8 and 32
+// (the forward kernels alone would take 8 on short alignments, the reverse kernel 16; one plan serves them all).
 static int segment_target(long long n_sites, int batch) {
+  (void)n_sites;
+  (void)batch;
   int target = 16;
-  if (n_sites > 0) {
-    const double warps = (double)((n_sites + 63) / 64) * (double)batch;  // warps of sites per walk launch
-    if (warps <= 400.0) {
-      const double ideal = (double)trex::sm_count() * 11.0 / warps;  // subtrees side by side that fill the GPU once
-      target = 8;
-      while (target * 1.5 < ideal && target < 64) target *= 2;
-    }
-  }
   if (const char* e = getenv("TREX_SEG_TARGET")) {  // experiments / tests
     const int v = atoi(e);
     if (v >= 1 && v <= trex::kMaxSeg) target = v;

@@ -97,10 +97,10 @@ __device__ __forceinline__ void pair_sweep(const float* __restrict__ rbase, cons
 // with 9-12 one-warp CTAs per SM some sub-partition hosts three warps and ptxas caps the kernel at 168 registers —
 // where this kernel spills and the dC sweep cannot be unrolled (every one of its 8 iterations then exposes a full
 // LDS latency: 17 % of the stall samples, profiles/r02_g_soft_bwd_uniform_hot_lines.txt).  At 8 CTAs per SM the cap
-// is 255: no spills and a 4x unrolled sweep whose loads run ahead of the FMAs.  Measured at 1024 taxa x 100k sites,
-// A = 20 (profiles/r02_h_soft_bwd_variants.txt): 8.30 -> 7.69 ms; at 12.5k sites (too few warps to fill the GPU
-// either way) 1.17 -> 1.37 ms, and without dC 5.11 -> 5.56 ms, so the launcher picks WIDE only for dC on long
-// alignments.
+// is 255: no spills, a 4x unrolled sweep whose loads run ahead of the FMAs, and room to keep the cotangent / r rows
+// of the row math in registers.  Measured at 1024 taxa x 100k sites, A = 20 (profiles/r02_h_soft_bwd_variants.txt):
+// 8.30 -> 6.74 ms; without dC the narrow build is the faster one (5.11 vs 5.56 ms: it needs no registers for the
+// sweep), so WIDE is the dC kernel only.
 template <int AP, int V, bool WANT_DC, bool FULL, bool WIDE = false>
 __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_uniform_kernel(const SoftBwdParams p) {
   using Cfg = UniCfg<AP, V>;
@@ -567,8 +567,10 @@ int launch_uniform(const SoftBwdParams& p0, int batch, cudaStream_t s) {
   };
   const SoftBwdParams& p = p0;
   const bool full = p.n_states == AP;
-  // long alignments (at least 4 warps of sites per SM): the 255-register build of the dC kernel
-  bool wide = AP > 8 && full && (long long)gx * batch >= 4LL * sm_count();  // measured: wins from 50k sites up, loses at 12.5k
+  // the 255-register build of the dC kernel: faster at every alignment length measured once its row math keeps the
+  // cotangent rows in registers (12.5k sites 1.16 -> 1.01 ms, 25k 2.27 -> 1.86, 100k 8.27 -> 6.74;
+  // profiles/r02_j_probe_step.txt)
+  bool wide = AP > 8 && full;
   if (const char* e = getenv("TREX_BWD_WIDE")) {  // tests: force the choice (the builds are parity-tested against each other's oracle)
     if (e[0] == '0' || e[0] == '1') wide = AP > 8 && full && e[0] == '1';
   }
