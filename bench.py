@@ -16,7 +16,8 @@ Sites are sharded over the ranks — STRONG scaling by default: the 100k sites o
 ways (the north-star case); `--scaling weak` gives every rank its own 100k sites, and at N > 1 a weak-scaling
 record is added to the line as `weak_scaling`.  One packed NCCL all-reduce per step combines the scalar costs,
 dC and the edge histogram.  The device-resident leg replays the step from a CUDA graph (the all-reduce is
-issued on the same stream after each replay); the e2e leg goes through trex_b200.pipeline.SankoffHostPipeline
+issued on a communication stream and overlaps the next step's kernels — steps are independent jobs — and every
+all-reduce is joined before the closing timing event); the e2e leg goes through trex_b200.pipeline.SankoffHostPipeline
 with pinned host inputs and host results (ancestral states + packed scalars) every step.
 """
 
@@ -616,13 +617,20 @@ class SankoffLeg:
     self.adj_d, self.cost_d = self.adj_p.cuda(), self.cost_p.cuda()
     self.eng = SankoffEngine(2 * n - 1, n, A, L)
     self.eng.set_leaf_states_u8(self.states_p.cuda())
-    self.reducer = PackedAllReduce([(1,), (1,), (1, A, A), (1, A, A)], device="cuda")
+    # two packed buffers alternate: the all-reduce of step k runs on a communication stream under the kernels of
+    # step k+1 (steps are independent jobs); both are joined before the closing timing event
+    self.reducers = [PackedAllReduce([(1,), (1,), (1, A, A), (1, A, A)], device="cuda") for _ in range(2)]
+    self.reducer = self.reducers[0]
+    self.comm = torch.cuda.Stream()
+    self.reduced = [None, None]
+    self.k = 0
     # Short alignments (a GPU's share under strong scaling) leave SMs idle in the top part of every walk and in
     # the wave tails: there the hard pass and the relaxed pass, which are independent, run on two streams.
     self.two_streams = L <= args.overlap_below
     self.side = (torch.cuda.Stream(), torch.cuda.Stream()) if self.two_streams else None
     self.stream = torch.cuda.Stream()
     self.graph = None
+    self.graphs = [None, None]
 
   def step_eager(self, ev=None):
     """single stream, optional event marks between the kernels"""
@@ -642,7 +650,8 @@ class SankoffLeg:
     self.reducer.pack([e.total, e.soft_total, e.dcost, e.edge_hist])
     mark(6)
 
-  def step_core(self):
+  def step_core(self, j=0):
+    self.reducer = self.reducers[j]
     if not self.two_streams:
       return self.step_eager()
     torch, e, c = self.torch, self.eng, self.cost_d
@@ -664,22 +673,44 @@ class SankoffLeg:
   def capture(self):
     torch = self.torch
     with torch.cuda.stream(self.stream):
-      self.step_core()
-      self.stream.synchronize()
-      if self.args.graph:
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, stream=self.stream):
-          self.step_core()
-        self.graph = g
+      for j in range(2):
+        self.step_core(j)
+        self.stream.synchronize()
+        if self.args.graph:
+          g = torch.cuda.CUDAGraph()
+          with torch.cuda.graph(g, stream=self.stream):
+            self.step_core(j)
+          self.graphs[j] = g
+      self.graph = self.graphs[0]
     torch.cuda.synchronize()
 
   def step(self):
-    """the timed step: graph replay (or eager launches) + the packed all-reduce, on self.stream"""
-    if self.graph is not None:
-      self.graph.replay()
+    """the timed step: graph replay (or eager launches) on self.stream, then the packed all-reduce of ITS results
+    on the communication stream (it overlaps the next step's kernels, which do not depend on it)"""
+    torch = self.torch
+    j = self.k & 1
+    self.k += 1
+    if self.reduced[j] is not None:
+      self.stream.wait_event(self.reduced[j])  # the pack of this step overwrites the buffer reduced two steps ago
+    if self.graphs[j] is not None:
+      self.graphs[j].replay()
     else:
-      self.step_core()
-    self.reducer.reduce()
+      self.step_core(j)
+    packed = torch.cuda.Event()
+    packed.record(self.stream)
+    with torch.cuda.stream(self.comm):
+      self.comm.wait_event(packed)
+      self.reducers[j].reduce()
+      done = torch.cuda.Event()
+      done.record(self.comm)
+    self.reduced[j] = done
+    self.last = j
+
+  def join(self):
+    """self.stream waits for every outstanding all-reduce (called before the closing timing event)"""
+    for ev in self.reduced:
+      if ev is not None:
+        self.stream.wait_event(ev)
 
   def timed(self, steps, warmup, barrier, sampler=None):
     torch = self.torch
@@ -687,12 +718,14 @@ class SankoffLeg:
     with torch.cuda.stream(self.stream):
       for _ in range(warmup):
         self.step()
+      self.join()
     barrier()
     t0 = time.perf_counter()
     with torch.cuda.stream(self.stream):
       e0.record(self.stream)
       for _ in range(steps):
         self.step()
+      self.join()
       e1.record(self.stream)
     barrier()
     if sampler is not None:
@@ -765,7 +798,7 @@ def run_gpu(args):
     sampler.start()
   ms_total = leg.timed(args.steps, args.warmup, barrier, sampler)
   clocks = sampler.stop() if rank == 0 else None
-  packed = leg.reducer.buf.cpu()
+  packed = leg.reducers[leg.last].buf.cpu()
   launches0 = int(lib.trex_kernel_launches())
   leg.step_eager()
   launches_per_step = int(lib.trex_kernel_launches()) - launches0

@@ -129,6 +129,11 @@ TREX_API int trex_sankoff_backtrack_ref(const float* bt_ref, int n_all, int n_le
                                int64_t n_sites, const int32_t* root_node, const int32_t* root_state,
                                int32_t* recon, void* stream);
 
+/* The library accumulates totals and dC in f64.  The reference runs with 64-bit types disabled
+ * (src/trex/types.py:12), so a jax.ffi binding cannot declare F64 results: this casts a small f64 vector to the
+ * f32 the reference returns (`total_cost` of sankoff.py:187 is an f32 sum).  dst[i] = (float)src[i]. */
+TREX_API int trex_cast_f64_to_f32(const double* src, float* dst, int64_t n, void* stream);
+
 /* ---- relaxed (softmin) Sankoff forward / reverse (not in the reference) --
  * min_t x -> -T*logsumexp_t(-x/T) in the recurrence of src/trex/sankoff.py:62-79 and :187.
  * Leaves: either `leaf_states` (u8, hard leaves = 1e5*(1-onehot)) or `leaf_cost`

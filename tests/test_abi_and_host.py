@@ -134,3 +134,34 @@ def test_site_sharded_reduction_world_size_2_gloo():
   for _, tot, full, hs in res:
     assert tot == full            # sum of shard scores == score of the whole alignment
     assert hs == 16 * (1 + 2)     # packed buffer reduced in the same single all-reduce
+
+
+def test_xla_ffi_shim_type_checks_and_matches_the_python_binding():
+  """The jax.ffi binding cannot run here (no jaxlib on any machine of this project: UNVERIFIED).
+  What can be checked: the shim's handler bodies type-check against a minimal mock of xla/ffi/api/ffi.h
+  (tests/mock_xla), every FFI target the Python side registers is defined by the shim, no handler returns F64
+  (the reference runs with x64 disabled, src/trex/types.py:12) and attributes are NumPy scalars, not jax Arrays."""
+  import re
+  import shutil
+  import subprocess
+
+  root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+  shim = os.path.join(root, "trex_b200", "csrc", "xla_ffi_shim.cc")
+  src = open(shim).read()
+  py = open(os.path.join(root, "trex_b200", "jax_ffi.py")).read()
+  gxx = shutil.which("g++")
+  if gxx:
+    cuda_inc = "/usr/local/cuda/include"
+    cmd = [gxx, "-std=c++17", "-fsyntax-only", "-Wall", "-Werror", "-I", os.path.join(root, "tests", "mock_xla")]
+    if os.path.isdir(cuda_inc):
+      cmd += ["-I", cuda_inc]
+      r = subprocess.run(cmd + [shim], capture_output=True, text=True)
+      assert r.returncode == 0, r.stderr[-2000:]
+  defined = set(re.findall(r"XLA_FFI_DEFINE_HANDLER_SYMBOL\((\w+),", src))
+  block = py[py.index("for _name in"):py.index("jax.ffi.register_ffi_target")]
+  registered = set(re.findall(r'"(trex_\w+_ffi)"', block))
+  called = set(re.findall(r'ffi_call\(\s*"(\w+)"', py))
+  assert registered == defined and called <= registered and registered
+  assert "Buffer<ffi::F64>>" not in src and "float64" not in py.split('"""', 2)[2]
+  assert not re.search(r"=\s*jnp\.(int|float)\d+\(", py)          # attributes: np.int32 / np.float32 ...
+  assert 'vmap_method="expand_dims"' in py

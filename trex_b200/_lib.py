@@ -35,6 +35,7 @@ SIGNATURES = {
   "trex_sankoff_export_recon": (_i, [_i, _i, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp]),
   "trex_sankoff_export_bt": (_i, [_vp, _i, _i, _i, _i64, _i64, _vp, _vp, _vp]),
   "trex_sankoff_backtrack_ref": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp]),
+  "trex_cast_f64_to_f32": (_i, [_vp, _vp, _i64, _vp]),
   "trex_sankoff_soft_fwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp]),
   "trex_sankoff_soft_bwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp]),
   "trex_sankoff_soft_bwd_compact": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -124,6 +124,12 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
   }
 }
 
+// f64 -> f32 cast of small result vectors (totals, dC) for bindings that run without 64-bit types
+__global__ void cast_f64_f32_kernel(const double* __restrict__ src, float* __restrict__ dst, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = (float)src[i];
+}
+
 // ---- exports -------------------------------------------------------------------------------
 // dp_ref[l][node][s] from dp[k][s][l]: 32x32 shared-memory transpose, both sides coalesced.
 __global__ void __launch_bounds__(256)
@@ -327,6 +333,16 @@ int trex_sankoff_backtrack_ref(const float* bt_ref, int n_all, int n_leaves, int
       bt_ref, n_all, n_leaves, n_states, n_sites, root_node, root_state, recon);
   note_launches(1);
   TREX_CHECK_LAUNCH("backtrack_ref_kernel");
+  return TREX_OK;
+}
+
+int trex_cast_f64_to_f32(const double* src, float* dst, int64_t n, void* stream) {
+  using namespace trex;
+  TREX_CHECK_ARG(src && dst && n >= 0, "trex_cast_f64_to_f32: bad arguments");
+  if (n == 0) return TREX_OK;
+  cast_f64_f32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(src, dst, (long long)n);
+  note_launches(1);
+  TREX_CHECK_LAUNCH("cast_f64_f32_kernel");
   return TREX_OK;
 }
 

@@ -6,9 +6,19 @@ container, so this module is UNTESTED there; the tested binding is t
 (``_lib.py`` + ``sankoff.py`` / ``tree.py``), which calls exactly the same C entry points.
 
 Each public function keeps the reference signature (``src/trex/sankoff.py:114-124``,
-``src/trex/tree.py:163-167, 212-217``), is ``jax.jit``/``vmap``/``grad`` compatible
-(``vmap_method="sequential"``; integer outputs get no cotangent) and is a thin
+``src/trex/tree.py:163-167, 212-217``), is ``jax.jit``/``vmap``/``grad`` compatible and is a thin
 ``jax.ffi.ffi_call`` under ``jax.custom_vjp``.  There is no fallback: import fails without JAX.
+
+Conventions (see the header of ``csrc/xla_ffi_shim.cc``):
+* ``vmap_method="expand_dims"``: mapped operands arrive with a leading batch dimension, unmapped ones with a
+  leading 1, so ``vmap`` over candidate trees with a shared alignment (``evals/benchmark.py:92-93``) is ONE
+  batched launch, not B sequential calls;
+* attributes are hashable NumPy scalars (``np.int32`` ...), never jax Arrays;
+* no float64 results — the reference runs with x64 disabled (``src/trex/types.py:12``): totals and dC come back
+  as float32 (accumulated in f64 inside the library).
+UNVERIFIED: never imported or lowered anywhere (no jaxlib on any machine of this project); where jaxlib exists,
+``python -c "import trex_b200.jax_ffi as t, jax; print(jax.jit(t.run_sankoff, static_argnames=(...)).lower(...))"``
+is the first check to run.
 """
 
 from __future__ import annotations
@@ -19,17 +29,25 @@ import os
 
 import jax
 import jax.numpy as jnp
+import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _FFI_LIB = os.path.join(_HERE, "libtrex_b200_ffi.so")
 
 _lib = ctypes.CDLL(_FFI_LIB)  # raises OSError when the shim was not built: no fallback
-for _name in ("trex_run_sankoff_ffi", "trex_soft_fwd_ffi", "trex_soft_bwd_ffi", "trex_tree_cost_ffi"):
+for _name in ("trex_run_sankoff_ffi", "trex_soft_fwd_ffi", "trex_soft_bwd_ffi", "trex_tree_cost_ffi",
+              "trex_fit_ancestors_ffi"):
   jax.ffi.register_ffi_target(_name, jax.ffi.pycapsule(getattr(_lib, _name)), platform="CUDA")
 
 
 def _pad16(n):
   return (n + 15) // 16 * 16
+
+
+def _plan_words(n_all, n_leaves):
+  """``trex_sankoff_plan_words`` (host-side query of the library: header + 9 words per internal node + 2 * 128)."""
+  _lib.trex_sankoff_plan_words.restype = ctypes.c_size_t
+  return int(_lib.trex_sankoff_plan_words(ctypes.c_int(n_all), ctypes.c_int(n_leaves)))
 
 
 @functools.partial(jax.jit, static_argnames=("return_path", "n_all", "n_states", "n_leaves"))
@@ -40,11 +58,11 @@ def run_sankoff(adjacency_matrix, cost_matrix, sequences, n_all, n_states, n_lea
   recon, dp, total = jax.ffi.ffi_call(
     "trex_run_sankoff_ffi",
     (jax.ShapeDtypeStruct((n_all, L), f32), jax.ShapeDtypeStruct((L, n_all, n_states), f32),
-     jax.ShapeDtypeStruct((1,), jnp.float64)),
-    vmap_method="sequential",
+     jax.ShapeDtypeStruct((), f32)),
+    vmap_method="expand_dims",
   )(adjacency_matrix.astype(f32), cost_matrix.astype(f32), sequences.astype(f32),
-    n_leaves=jnp.int32(n_leaves), return_path=bool(return_path))
-  return recon, dp, total[0].astype(f32)
+    n_leaves=np.int32(n_leaves), return_path=bool(return_path))
+  return recon, dp, total
 
 
 def _tree_cost_call(sequences, adjacency, cost_matrix):
@@ -56,8 +74,8 @@ def _tree_cost_call(sequences, adjacency, cost_matrix):
     "trex_tree_cost_ffi",
     (jax.ShapeDtypeStruct((), f32), jax.ShapeDtypeStruct((N, L, Q), f32), jax.ShapeDtypeStruct((N, N), f32),
      jax.ShapeDtypeStruct(c.shape, f32)),
-    vmap_method="sequential",
-  )(sequences.astype(f32), adjacency.astype(f32), c, cost_kind=jnp.int32(kind))
+    vmap_method="expand_dims",
+  )(sequences.astype(f32), adjacency.astype(f32), c, cost_kind=np.int32(kind))
 
 
 @jax.custom_vjp
@@ -87,7 +105,7 @@ def compute_surrogate_cost(sequences, adjacency):
 @functools.partial(jax.custom_vjp, nondiff_argnums=(3, 4, 5))
 def soft_sankoff_cost(adjacency_matrix, cost_matrix, leaf_cost_native, n_leaves, n_sites, temperature):
   """Relaxed parsimony score; ``leaf_cost_native`` is [n_leaves][A][pad16(L)] f32."""
-  return _soft_fwd(adjacency_matrix, cost_matrix, leaf_cost_native, n_leaves, n_sites, temperature)[2][0]
+  return _soft_fwd(adjacency_matrix, cost_matrix, leaf_cost_native, n_leaves, n_sites, temperature)[2]
 
 
 def _soft_fwd(adj, cost, leaf_cost, n_leaves, n_sites, temperature):
@@ -95,16 +113,16 @@ def _soft_fwd(adj, cost, leaf_cost, n_leaves, n_sites, temperature):
   n_int = n_all - n_leaves
   return jax.ffi.ffi_call(
     "trex_soft_fwd_ffi",
-    (jax.ShapeDtypeStruct((8 + 9 * n_int + 256,), jnp.int32), jax.ShapeDtypeStruct((n_int, A, stride), jnp.float32),
-     jax.ShapeDtypeStruct((1,), jnp.float64)),
-    vmap_method="sequential",
-  )(adj.astype(jnp.float32), cost.astype(jnp.float32), leaf_cost, n_leaves=jnp.int32(n_leaves),
-    n_sites=jnp.int64(n_sites), temperature=jnp.float32(temperature))
+    (jax.ShapeDtypeStruct((_plan_words(n_all, n_leaves),), jnp.int32),
+     jax.ShapeDtypeStruct((n_int, A, stride), jnp.float32), jax.ShapeDtypeStruct((), jnp.float32)),
+    vmap_method="expand_dims",
+  )(adj.astype(jnp.float32), cost.astype(jnp.float32), leaf_cost, n_leaves=np.int32(n_leaves),
+    n_sites=np.int64(n_sites), temperature=np.float32(temperature))
 
 
 def _ssc_fwd(adj, cost, leaf_cost, n_leaves, n_sites, temperature):
   plan, dp, total = _soft_fwd(adj, cost, leaf_cost, n_leaves, n_sites, temperature)
-  return total[0], (plan, dp, cost, leaf_cost, adj.shape[0])
+  return total, (plan, dp, cost, leaf_cost, adj.shape[0])
 
 
 def _ssc_bwd(n_leaves, n_sites, temperature, res, g):
@@ -114,12 +132,34 @@ def _ssc_bwd(n_leaves, n_sites, temperature, res, g):
   _, dleaf, dcost = jax.ffi.ffi_call(
     "trex_soft_bwd_ffi",
     (jax.ShapeDtypeStruct((n_int, A, stride), jnp.float32), jax.ShapeDtypeStruct(leaf_cost.shape, jnp.float32),
-     jax.ShapeDtypeStruct((A, A), jnp.float64)),
-    vmap_method="sequential",
+     jax.ShapeDtypeStruct((A, A), jnp.float32)),
+    vmap_method="expand_dims",
   )(plan, cost.astype(jnp.float32), leaf_cost, dp, jnp.asarray(g, jnp.float32).reshape(1),
-    n_all=jnp.int32(n_all), n_leaves=jnp.int32(n_leaves), n_sites=jnp.int64(n_sites),
-    temperature=jnp.float32(temperature))
+    n_all=np.int32(n_all), n_leaves=np.int32(n_leaves), n_sites=np.int64(n_sites),
+    temperature=np.float32(temperature))
   return jnp.zeros((n_all, n_all), jnp.float32), dcost.astype(cost.dtype), dleaf
 
 
 soft_sankoff_cost.defvjp(_ssc_fwd, _ssc_bwd)
+
+
+_OPTIMIZERS = {"adam": 0, "sgd": 1, "rmsprop": 2, "adamw": 3}  # TREX_OPT_* (include/trex_b200.h)
+
+
+@functools.partial(jax.jit, static_argnames=("optimizer", "learning_rate", "clip_norm", "n_iterations"))
+def fit_ancestors(adjacency, leaf_seqs, ancestor_logits, optimizer="adam", learning_rate=1e-3, clip_norm=1.0,
+                  n_iterations=10_000):
+  """The loop of ``run_trex_optimization_configurable`` (``src/trex/evals/benchmark.py:75-200``) as one call:
+  returns ``(logits (n_anc,L,Q) f32, losses (n_iterations,) f32, argmax (n_anc,L) i32)``.  Not vmapped."""
+  f32 = jnp.float32
+  n_anc, L, Q = ancestor_logits.shape
+  out, _, _, losses, argmax = jax.ffi.ffi_call(
+    "trex_fit_ancestors_ffi",
+    (jax.ShapeDtypeStruct((n_anc, L, Q), f32), jax.ShapeDtypeStruct((n_anc, L, Q), f32),
+     jax.ShapeDtypeStruct((n_anc, L, Q), f32), jax.ShapeDtypeStruct((n_iterations,), f32),
+     jax.ShapeDtypeStruct((n_anc, L), jnp.int32)),
+    vmap_method="sequential",
+  )(adjacency.astype(f32), leaf_seqs.astype(f32), ancestor_logits.astype(f32),
+    optimizer=np.int32(_OPTIMIZERS[optimizer]), learning_rate=np.float32(learning_rate),
+    clip_norm=np.float32(clip_norm), n_iterations=np.int32(n_iterations))
+  return out, losses, argmax
