@@ -48,6 +48,11 @@ extern "C" {
 /* plan status bits (word 3 of each tree's plan header) */
 #define TREX_PLAN_HAS_SENTINEL_CHILD 1 /* some node has < 2 children, or a child id >= its own */
 #define TREX_PLAN_NOT_A_TREE 2         /* a node is the child of two parents; index order used */
+#define TREX_PLAN_SHARED_LEAF 4        /* a leaf is the child of two parents (or listed twice) */
+/* The forward passes accept such adjacencies and match the reference on them.  The relaxed REVERSE pass is defined
+ * for trees only (it stores each child's cotangent row once instead of accumulating): when bit 2 or 4 is set,
+ * trex_sankoff_soft_bwd / _compact write NaN into every entry of `dcost` (when given), so the condition is visible
+ * in the results without a host synchronisation; gbar / dleaf are then unspecified. */
 
 TREX_API const char* trex_last_error(void);
 TREX_API int trex_version(void);
@@ -146,7 +151,8 @@ TREX_API int trex_sankoff_soft_fwd(const int32_t* plan, int n_all, int n_leaves,
                           float temperature, float* dp, double* total, void* stream);
 /*   gscale  device f32 scalar (upstream cotangent) or NULL = 1
  *   gbar    [batch][n_int][A][site_stride] f32 out: d total / d dp[node] = soft ancestral marginals
- *   dleaf   [batch][n_leaves][A][site_stride] f32 out or NULL: d total / d leaf_cost
+ *   dleaf   [batch][n_leaves][A][site_stride] f32 out or NULL: d total / d leaf_cost (rows of leaves under nodes
+ *           the root does not reach are written as zeros; rows of leaves that are no node's child are not written)
  *   dcost   [batch][A][A] f64 out or NULL */
 TREX_API int trex_sankoff_soft_bwd(const int32_t* plan, int n_all, int n_leaves, int n_states,
                           int64_t n_sites, int64_t site_stride, int batch,

@@ -235,3 +235,105 @@ def test_full_size_relaxed_properties(n, A, L):
   assert float((g0 - g1).abs().max()) <= 2 * RTOL
   assert float((dl0 - dl1).abs().max()) <= 2 * RTOL
   assert float((dc0 - dc1).abs().max()) <= RTOL * float(dc0.abs().max())
+
+
+def _subtree_leaves(par, k, n):
+  kids = [v for v in range(len(par)) if par[v] == k]
+  out = []
+  for v in kids:
+    out += [v] if v < n else _subtree_leaves(par, v, n)
+  return out
+
+
+@pytest.mark.parametrize("ck,A,T", [("unit", 20, 1.0), ("int", 20, 1.0), ("unit", 4, 0.5), ("int", 5, 0.01)])
+@pytest.mark.parametrize("compact", [False, True])
+def test_reverse_pass_on_a_forest_zeroes_the_unreached_rows(ck, A, T, compact):
+  """A subtree detached from the root (its parent is left with one child — the -1 fill of sankoff.py:60): the
+  cotangents of its nodes and the leaf-gradient rows of its leaves are ZERO (written, not left stale), everything
+  reachable matches the oracle."""
+  import torch
+  from trex_b200.sankoff import SankoffEngine
+
+  n, L = 12, 70
+  rng = np.random.default_rng(A + int(10 * T))
+  par = synth.random_join_parents(n, rng)
+  n_all = 2 * n - 1
+  cand = [k for k in range(n, n_all - 1) if len(_subtree_leaves(par, k, n)) >= 2]
+  k = cand[len(cand) // 2]
+  adj = synth.parents_to_adjacency(par)
+  adj[k, par[k]] = 0                                  # detach internal node k
+  lost = _subtree_leaves(par, k, n)
+  states = synth.evolve(par, L, A, 0.2, rng)
+  cost = synth.unit_cost(A) if ck == "unit" else synth.random_int_cost(A, 5, rng)
+  lc = so.leaf_cost_from_states(states[:n], A)
+  dp64, tot64 = so.soft_sankoff_fwd(adj, cost, lc, n_all, n, T)
+  g64, dC64 = so.soft_sankoff_bwd(adj, cost, dp64, n_all, n, T)
+  eng = SankoffEngine(n_all, n, A, L)
+  eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states[:n]))
+  eng.soft_forward(torch.from_numpy(cost), T)
+  assert abs(float(eng.soft_total[0]) - tot64) <= RTOL * abs(tot64)
+  eng.gbar.fill_(float("nan"))
+  eng.dleaf.fill_(float("nan"))
+  eng.dleaf_obs.fill_(float("nan"))
+  eng.soft_backward(torch.from_numpy(cost), T, want_dleaf="compact" if compact else True)
+  gbar = eng.gbar[0, :, :, :L].permute(2, 0, 1).cpu().numpy()
+  # The parent of the detached node is left with a missing child = the reference's all-1e5 row (sankoff.py:60,152),
+  # so every dp row above it is ~1e5: float32 resolves that to 2^-7, and the softmin weights exp(-(x - m)/T) of ANY
+  # float32 evaluation move by 2^-24 * max|dp| / T (same clause as tests/test_gpu_bench_shapes.py).
+  gtol = max(RTOL, 2.0 ** -24 * np.abs(dp64[:, n:]).max() / T)
+  assert not np.isnan(gbar).any()
+  assert np.all(gbar[:, k - n] == 0.0)                 # the detached subtree: exact zeros, written by the kernel
+  assert np.abs(gbar - g64[:, n:]).max() <= gtol
+  assert _relerr(eng.dcost[0].cpu().numpy(), dC64) <= gtol
+  if compact:
+    obs = eng.dleaf_obs[0, :, :L].cpu().numpy()
+    assert np.all(obs[lost] == 0.0)
+    assert np.abs(obs - g64[:, :n].sum(axis=2).T).max() <= gtol
+  else:
+    dleaf = eng.dleaf[0, :, :, :L].permute(2, 0, 1).cpu().numpy()
+    assert np.all(dleaf[:, lost] == 0.0)
+    assert np.abs(dleaf - g64[:, :n]).max() <= gtol
+
+
+@pytest.mark.parametrize("ck,A,T", [("unit", 20, 1.0), ("int", 20, 1.0), ("int", 5, 0.01)])
+@pytest.mark.parametrize("kind", ["shared_leaf", "shared_node"])
+def test_reverse_pass_poisons_dcost_when_the_adjacency_is_not_a_tree(ck, A, T, kind):
+  """A leaf or an internal node with two parents: the forward passes still match the reference semantics (and the
+  oracle); the reverse pass is defined on trees only and says so in its result — every entry of dC is NaN, with
+  no host synchronisation needed to find out (include/trex_b200.h, TREX_PLAN_NOT_A_TREE / TREX_PLAN_SHARED_LEAF)."""
+  import torch
+  from trex_b200 import _lib
+  from trex_b200.sankoff import SankoffEngine
+
+  n, L = 10, 40
+  rng = np.random.default_rng(3)
+  par = synth.random_join_parents(n, rng)
+  n_all = 2 * n - 1
+  adj = synth.parents_to_adjacency(par)
+  if kind == "shared_leaf":
+    victim = 0
+    other = next(k for k in range(n, n_all) if k != par[victim] and np.count_nonzero(adj[:, k]) == 2)
+    donor = int(np.nonzero(adj[:, other])[0][-1])
+    adj[donor, other] = 0                            # `other` now takes leaf 0 as a child as well
+    adj[victim, other] = 1
+  else:
+    victim = next(k for k in range(n, n_all - 2) if par[k] < n_all - 1)
+    other = next(k for k in range(victim + 1, n_all) if k != par[victim])
+    donor = int(np.nonzero(adj[:, other])[0][-1])
+    adj[donor, other] = 0
+    adj[victim, other] = 1
+  states = synth.evolve(par, L, A, 0.2, rng)
+  cost = synth.unit_cost(A) if ck == "unit" else synth.random_int_cost(A, 5, rng)
+  eng = SankoffEngine(n_all, n, A, L)
+  eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states[:n]))
+  _, status = eng.plan_status()
+  assert status & (_lib.PLAN_NOT_A_TREE | _lib.PLAN_SHARED_LEAF)
+  # forward passes: unchanged semantics
+  tabs = so.run_sankoff_tables(adj, cost, states[:n], n_all, A, n)
+  eng.hard_forward(torch.from_numpy(cost))
+  assert np.array_equal(eng.export_dp().cpu().numpy(), tabs["dp"])
+  dp64, tot64 = so.soft_sankoff_fwd(adj, cost, so.leaf_cost_from_states(states[:n], A), n_all, n, T)
+  eng.soft_forward(torch.from_numpy(cost), T)
+  assert abs(float(eng.soft_total[0]) - tot64) <= RTOL * abs(tot64)
+  eng.soft_backward(torch.from_numpy(cost), T, want_dleaf="compact")
+  assert bool(torch.isnan(eng.dcost[0]).all())

@@ -16,6 +16,7 @@ MODE_AUTO = 0
 MODE_GENERAL = 1
 PLAN_HAS_SENTINEL_CHILD = 1
 PLAN_NOT_A_TREE = 2
+PLAN_SHARED_LEAF = 4
 PLAN_HDR = 8
 
 _vp, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float

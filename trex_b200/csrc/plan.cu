@@ -117,6 +117,7 @@ __global__ void __launch_bounds__(kColsPerCta* kRowChunks)
 // ordered steps (numbering the segments, compacting the top list) are light single-thread loops.
 constexpr int kSmemNodes = 8192;  // 6 int32 arrays of this many nodes = 192 KB of dynamic shared memory
 constexpr int kPlanThreads = 256;
+constexpr int kLeafSeenWords = 1024;  // shared-leaf detection covers the first 32 768 leaves
 
 __global__ void __launch_bounds__(kPlanThreads)
     plan_order_kernel(int n_all, int n_leaves, int32_t* __restrict__ plan, size_t plan_words, int use_smem,
@@ -149,6 +150,8 @@ __global__ void __launch_bounds__(kPlanThreads)
   }
   __shared__ int s_hdr[8];
   __shared__ int s_status;
+  __shared__ unsigned s_leaf_seen[kLeafSeenWords];  // one bit per leaf: already the child of some node
+  for (int w = tid; w < kLeafSeenWords; w += kPlanThreads) s_leaf_seen[w] = 0u;
   if (tid == 0) s_status = 0;
   for (int k = tid; k < n_int; k += kPlanThreads) { size[k] = 0; off[k] = -1; par[k] = -1; }
   __syncthreads();
@@ -159,6 +162,13 @@ __global__ void __launch_bounds__(kPlanThreads)
     if (a < 0 || b < 0) st |= TREX_PLAN_HAS_SENTINEL_CHILD;
     if (a >= n_leaves && atomicExch(&par[a - n_leaves], k) != -1) st |= TREX_PLAN_NOT_A_TREE;
     if (b >= n_leaves && atomicExch(&par[b - n_leaves], k) != -1) st |= TREX_PLAN_NOT_A_TREE;
+    // a leaf with two parents (or listed twice): harmless for the forward pass, but the reverse kernels STORE a
+    // leaf's gradient row instead of accumulating it
+    for (int c : {a, b})
+      if (c >= 0 && c < n_leaves && c < 32 * kLeafSeenWords) {
+        const unsigned bit = 1u << (c & 31);
+        if (atomicOr(&s_leaf_seen[c >> 5], bit) & bit) st |= TREX_PLAN_SHARED_LEAF;
+      }
     if (st) atomicOr(&s_status, st);
   }
   __syncthreads();

@@ -117,8 +117,16 @@ __global__ void __launch_bounds__(THREADS) soft_bwd_kernel(const SoftBwdParams p
 #pragma unroll
     for (int v = 0; v < V; ++v) zero[v] = 0.f;
     for (int i = n_reach; i < n_int; ++i) {
-      float* row = gbar + (size_t)(__ldg(order + i) - p.n_leaves) * A * p.stride;
+      const int ku = __ldg(order + i) - p.n_leaves;
+      float* row = gbar + (size_t)ku * A * p.stride;
       for (int s = 0; s < A; ++s) st_f<V>(row + (size_t)s * p.stride, zero);
+      for (int slot = 0; slot < 2; ++slot) {  // ... and so do the leaf-gradient rows of their leaf children
+        const int c = __ldg(plan.child(slot) + ku);
+        if (c < 0 || c >= p.n_leaves) continue;
+        if (dleaf)
+          for (int s = 0; s < A; ++s) st_f<V>(dleaf + ((size_t)c * A + s) * p.stride, zero);
+        if (dleaf_obs) st_f<V>(dleaf_obs + (size_t)c * p.stride, zero);
+      }
     }
     // root cotangent: gscale * softmax_s(-dp[root]/T)
     float x[AP][V];
@@ -366,6 +374,9 @@ __global__ void __launch_bounds__(THREADS) soft_bwd_kernel(const SoftBwdParams p
         if (v != 0.f) atomicAdd(p.dcost + (size_t)tree * A * A + i, (double)v);
       }
     }
+    // reverse mode is defined on trees only (include/trex_b200.h, TREX_PLAN_NOT_A_TREE / _SHARED_LEAF): poison dC
+    if (blockIdx.x == 0 && (plan.hdr()[3] & (TREX_PLAN_NOT_A_TREE | TREX_PLAN_SHARED_LEAF)))
+      for (int i = tid; i < A * A; i += THREADS) atomicAdd(p.dcost + (size_t)tree * A * A + i, (double)NAN);
   }
 }
 

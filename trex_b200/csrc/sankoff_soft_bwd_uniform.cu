@@ -208,8 +208,16 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
     for (int v = 0; v < V; ++v) zero[v] = 0.f;
     if (active) {
       for (int i = plan.hdr()[1]; i < n_int; ++i) {
-        float* row = gbar + (size_t)(__ldg(plan.order() + i) - p.n_leaves) * A * stride;
+        const int ku = __ldg(plan.order() + i) - p.n_leaves;
+        float* row = gbar + (size_t)ku * A * stride;
         for (int s = 0; s < A; ++s) st_f<V>(row + s * stride, zero);
+        for (int slot = 0; slot < 2; ++slot) {  // ... and so do the leaf-gradient rows of their leaf children
+          const int c = __ldg(plan.child(slot) + ku);
+          if (c < 0 || c >= p.n_leaves) continue;
+          if (dleaf)
+            for (int s = 0; s < A; ++s) st_f<V>(dleaf + ((size_t)c * A + s) * stride, zero);
+          if (dleaf_obs) st_f<V>(dleaf_obs + (size_t)c * stride, zero);
+        }
       }
     }
     const float* rrow = dp + (size_t)(n_int - 1) * A * stride;
@@ -535,8 +543,9 @@ __global__ void __launch_bounds__(32, AP > 8 ? (WIDE ? 8 : 11) : 16) soft_bwd_un
   }
   if constexpr (WANT_DC) {
     __syncwarp();
+    const bool not_tree = (plan.hdr()[3] & (TREX_PLAN_NOT_A_TREE | TREX_PLAN_SHARED_LEAF)) != 0;
     for (int i = lane; i < A * A; i += 32) {
-      const double v = sAcc[(i / A) * AP + i % A];
+      const double v = not_tree ? (double)NAN : sAcc[(i / A) * AP + i % A];  // reverse mode is defined on trees only
       if (v != 0.0) atomicAdd(p.dcost + (size_t)tree * A * A + i, v);
     }
   }
