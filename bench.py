@@ -510,6 +510,42 @@ def general_cost_bench(torch, eng, peak):
   return out
 
 
+def generators_bench(torch):
+  """the c5 inputs produced ON THE DEVICE (no host arrays, no H2D): generate_groundtruth
+  (ground_truth.py:113-197; fixed-count mutation tree, 1024 leaves x 100k sites, A = 20, 5000 mutations per edge) and
+  the NK-landscape variant c5 names (nk_model.py:17-278 with the parameters of evals/benchmark.py:922-929: K = 1,
+  q = 20, mutation_rate 0.1, coupled_mutation_prob 0.5, branch_length 1; fitness table 400 x 100k f32 = 160 MB), then
+  scored by the hard Sankoff pass to show the states feed the engine directly.  Philox draws (jax.random's streams
+  are not reproducible outside JAX); parity on explicit draws is tests/test_gpu_generators.py."""
+  from trex_b200 import generators as G
+  from trex_b200 import synth
+  from trex_b200.sankoff import SankoffEngine
+
+  n, A, L = N_LEAVES, N_STATES, N_SITES
+  out = {}
+  gt = G.generate_groundtruth(n, A, 5000, L, seed=5)
+  out["groundtruth_ms"] = event_ms(torch, lambda: G.generate_groundtruth(n, A, 5000, L, seed=5), 3, warm=1)
+  land = G.create_nk_model_landscape(L, 1, seed=5, n_states=A)
+  adj = G.create_balanced_binary_tree(n)
+  root = torch.randint(0, A, (L,), device="cuda", dtype=torch.uint8)
+  out["nk_landscape_ms"] = event_ms(torch, lambda: G.create_nk_model_landscape(L, 1, seed=5, n_states=A), 3, warm=1)
+  nk = G.generate_tree_data(land, adj, root, 0.1, seed=5, coupled_mutation_prob=0.5, n_states=A)
+  out["nk_tree_ms"] = event_ms(torch, lambda: G.generate_tree_data(land, adj, root, 0.1, seed=5, coupled_mutation_prob=0.5,
+                                                                   n_states=A), 3, warm=1)
+  cost = torch.from_numpy(synth.unit_cost(A)).cuda()
+  for name, tree, a in (("groundtruth", gt, gt.adjacency), ("nk", nk, adj)):
+    eng = SankoffEngine(2 * n - 1, n, A, L)
+    eng.set_adjacency(a)
+    eng.leaf.copy_(tree.states_u8[:n])          # device-to-device: the generated states are the engine's input format
+    if eng.leaf.shape[1] > L:
+      eng.leaf[:, L:].fill_(255)
+    out[name + "_parsimony_score"] = float(eng.hard_forward(cost, want_argmin=False)[0])
+    del eng
+    torch.cuda.empty_cache()
+  out["shape"] = f"{n} leaves x {L} sites, A = {A}"
+  return out
+
+
 def c4_bench(torch, dist, world, rank, reps=5):
   """BASELINE config c4: batched (vmap-over-trees, evals/benchmark.py:92-93) scoring of 512 candidate trees,
   128 taxa x 5000 sites, A in {4, 20}, unit cost; the tree batch is sharded over the ranks
@@ -902,6 +938,7 @@ def run_gpu(args):
     if world == 1 and not args.no_extras:
       if L == N_SITES:
         line["general_cost"] = general_cost_bench(torch, leg.eng, peak)
+      line["generators"] = generators_bench(torch)
       line["tree_cost"] = tree_cost_bench(torch)
       line["fit_loop"] = fit_loop_bench(torch)
       line["landscape_loss"] = landscape_bench(torch)

@@ -278,6 +278,54 @@ TREX_API int trex_landscape_loss_fwd_bwd(const float* seqs, const float* adjacen
                                 float* out_logits, float* d_seqs, int32_t* parent_scratch, double* acc_scratch,
                                 void* stream);
 
+/* ---- on-device input generators ---------------------------------------------------------
+ * Random draws: jax.random (threefry) streams cannot be reproduced outside JAX, so every generator takes its draws
+ * either as EXPLICIT device arrays (the parity tests feed the same arrays to the NumPy restatement of the reference
+ * code and demand identical results) or, when the draw pointers are NULL, from a counter-based Philox4x32-10 stream
+ * keyed by `seed` (reproducible; not JAX's stream).  State tables are u8 [node][site_stride].
+ *
+ * create_balanced_binary_tree (src/trex/evals/benchmark.py:781-791; kind 1) and the adjacency of
+ * generate_groundtruth (src/trex/ground_truth.py:180-191; kind 0): adjacency [n_all][n_all] f32, no root self-loop. */
+TREX_API int trex_tree_adjacency(int n_leaves, int kind, float* adjacency, void* stream);
+/* generate_groundtruth (src/trex/ground_truth.py:113-197) with mutate (:20-53): root sequence all zeros, every node's
+ * two children (2 p_i, 2 p_i + 1 of parent n_leaves + p_i) are the parent with `n_mutations` distinct sites moved to
+ * (state + offset) % n_states, offset in 1..n_states-1.  n_leaves must be a power of two (the reference raises
+ * ValueError, :142-144; here TREX_ERR_INVALID_ARGUMENT).
+ *   mut_sites  [n_all-1][n_mutations] i32 or NULL: the sites each edge (= child node) mutates (negative wrap, OOB dropped)
+ *   offsets    [n_all-1][n_sites] u8 or NULL:      the offset draw of every (edge, site)
+ *   all_states [n_all][site_stride] u8 out (rows < n_leaves are the leaves = the reference's masked_sequences rows)
+ *   adjacency  [n_all][n_all] f32 out or NULL */
+TREX_API size_t trex_generate_groundtruth_workspace_bytes(int n_leaves, int n_mutations, int64_t n_sites);
+TREX_API int trex_generate_groundtruth(int n_leaves, int n_states, int n_mutations, int64_t n_sites, int64_t site_stride,
+                              uint64_t seed, const int32_t* mut_sites, const uint8_t* offsets, uint8_t* all_states,
+                              float* adjacency, void* workspace, void* stream);
+/* create_nk_model_landscape (src/trex/nk_model.py:17-43): interactions [n][k] i32 ~ randint(0, n) (may be NULL when k == 0),
+ * fitness_tables [n][n_states^(k+1)] f32 ~ U[0,1). */
+TREX_API int trex_nk_landscape(int64_t n, int k, int n_states, uint64_t seed, int32_t* interactions, float* fitness_tables,
+                      void* stream);
+/* get_fitness / batched_get_fitness (src/trex/nk_model.py:46-113): out[b] = sum_i mask_i f_i(seq_i, partners) / sum mask;
+ * seqs [batch][seq_stride] u8, seq_mask [n] f32 or NULL. */
+TREX_API int trex_nk_fitness(const uint8_t* seqs, int64_t seq_stride, int batch, int64_t n, int k, int n_states,
+                    const int32_t* interactions, const float* fitness_tables, const float* seq_mask, float* out_fitness,
+                    void* stream);
+/* generate_tree_data (src/trex/nk_model.py:116-278): Metropolis-Hastings evolution down the tree, `branch_length` steps
+ * per edge, each a coupled mutation (one site + its k partners redrawn, probability coupled_mutation_prob) or a random
+ * mutation (every site redrawn with the edge's rate = min(1, mutation_rate * exp(N(0,1) * noise_std))), accepted with
+ * probability min(1, exp(fitness(proposal) - fitness(current))).  Parents = argmax of each adjacency row.
+ * ROOT: the reference takes "the node that is its own argmax", which needs a root self-loop; without one (the
+ * adjacency of its own callers) it falls back to node 0 and produces a degenerate tree.  That defect is not
+ * reproduced: here a node whose row has no positive entry is a root too.
+ *   draw_noise [N]; draw_u_coupled / draw_site / draw_u_accept [N][branch_length]; draw_u_mask (f32) / draw_new_vals (u8)
+ *   [N][branch_length][n_sites] — each may be NULL (Philox).  all_states [N][site_stride] u8 out. */
+TREX_API size_t trex_nk_generate_tree_workspace_bytes(int n_nodes, int64_t site_stride);
+TREX_API int trex_nk_generate_tree(const float* adjacency, int n_nodes, const uint8_t* root_sequence, int64_t n_sites,
+                          int64_t site_stride, int k, int n_states, const int32_t* interactions,
+                          const float* fitness_tables, float mutation_rate, float coupled_mutation_prob,
+                          float mutation_rate_noise_std, int branch_length, uint64_t seed, const float* draw_noise,
+                          const float* draw_u_coupled, const int32_t* draw_site, const float* draw_u_mask,
+                          const uint8_t* draw_new_vals, const float* draw_u_accept, uint8_t* all_states, void* workspace,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -164,6 +164,44 @@ def _gumbel(key, shape=(), dtype=np.float32):
   return _wrap(g)
 
 
+# Recording random functions (make_golden_generators.py): jax.random's threefry streams are not reproducible without
+# JAX, so each call draws from NumPy and appends (function name, array) to DRAWS in CALL ORDER; the golden script
+# maps that log onto the explicit draw arrays the oracle and the CUDA generators take.  bernoulli is `uniform < p`
+# (as in jax) and logs the uniform.
+DRAWS = []
+
+
+def _rec(name, arr):
+  DRAWS.append((name, np.array(arr)))
+  return arr
+
+
+def _r_choice(key, a, shape=(), replace=True, p=None):
+  n = int(np.prod(shape)) if shape != () else 1
+  out = _RNG.choice(int(a) if np.ndim(a) == 0 else np.asarray(a), size=n, replace=replace, p=p).reshape(shape)
+  return _wrap(_rec("choice", out))
+
+
+def _r_randint(key, shape, minval, maxval, dtype=np.int32):
+  return _wrap(_rec("randint", _RNG.integers(minval, maxval, size=shape).astype(dtype)))
+
+
+def _r_uniform(key, shape=(), dtype=np.float32, minval=0.0, maxval=1.0):
+  return _wrap(_rec("uniform", (_RNG.random(size=shape) * (maxval - minval) + minval).astype(dtype)))
+
+
+def _r_bernoulli(key, p=0.5, shape=None):
+  shape = np.shape(p) if shape is None else shape
+  u = _rec("bernoulli_uniform", _RNG.random(size=shape).astype(np.float32))
+  r = u < np.asarray(p)
+  return _wrap(np.asarray(r)) if np.ndim(r) else bool(r)
+
+
+def _r_normal(key, shape=(), dtype=np.float32):
+  r = _rec("normal", np.asarray(_RNG.normal(size=shape)).astype(dtype))
+  return _wrap(r) if np.ndim(r) else np.float32(r)
+
+
 def install():
   """Register the stand-in as ``jax`` / ``jax.numpy`` / ``jax.lax`` / ``jax.nn`` / ``jax.random``."""
   if "jax" in sys.modules and not getattr(sys.modules["jax"], "_IS_NUMPY_SHIM", False):
@@ -173,7 +211,7 @@ def install():
   jnp = types.ModuleType("jax.numpy")
   for name in ["zeros", "ones", "full", "arange", "eye", "stack", "concatenate", "zeros_like", "ones_like",
                "array", "asarray", "isnan", "isclose", "allclose", "log", "exp", "einsum", "broadcast_to",
-               "transpose", "sqrt", "abs", "mean"]:
+               "transpose", "sqrt", "abs", "mean", "roll", "append", "dot", "squeeze", "minimum", "maximum"]:
     def mk(fn):
       return lambda *a, **k: _wrap(fn(*a, **k))
     setattr(jnp, name, mk(getattr(np, name)))
@@ -200,6 +238,8 @@ def install():
   random.PRNGKey = random.key = lambda seed: _wrap(np.array([0, seed], dtype=np.uint32))
   random.split = lambda key, num=2: _wrap(np.stack([np.asarray(key)] * num))
   random.gumbel = _gumbel
+  random.choice, random.randint, random.uniform = _r_choice, _r_randint, _r_uniform
+  random.bernoulli, random.normal = _r_bernoulli, _r_normal
   debug = types.ModuleType("jax.debug")
   debug.print = lambda *a, **k: None
   tree_util = types.ModuleType("jax.tree_util")

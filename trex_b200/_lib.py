@@ -52,6 +52,14 @@ SIGNATURES = {
   "trex_compute_cost_noalloc_scratch_bytes": (C.c_size_t, []),
   "trex_compute_cost_noalloc": (_i, [_vp, _vp, _vp, _i, _i64, _i, _vp, _vp]),
   "trex_landscape_loss_fwd_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+  "trex_tree_adjacency": (_i, [_i, _i, _vp, _vp]),
+  "trex_generate_groundtruth_workspace_bytes": (C.c_size_t, [_i, _i, _i64]),
+  "trex_generate_groundtruth": (_i, [_i, _i, _i, _i64, _i64, C.c_uint64, _vp, _vp, _vp, _vp, _vp, _vp]),
+  "trex_nk_landscape": (_i, [_i64, _i, _i, C.c_uint64, _vp, _vp, _vp]),
+  "trex_nk_fitness": (_i, [_vp, _i64, _i, _i64, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+  "trex_nk_generate_tree_workspace_bytes": (C.c_size_t, [_i, _i64]),
+  "trex_nk_generate_tree": (_i, [_vp, _i, _vp, _i64, _i64, _i, _i, _vp, _vp, _f, _f, _f, _i, C.c_uint64, _vp, _vp, _vp, _vp,
+                                 _vp, _vp, _vp, _vp, _vp]),
   "trex_fit_ancestors_workspace_bytes": (C.c_size_t, [_i, _i, _i64, _i]),
   "trex_fit_ancestors": (_i, [_vp, _vp, _i, _i, _i64, _i, _vp, _vp, _vp, _i, _f, _f, _i, _i64, _vp, _vp, _vp, _vp]),
 }
