@@ -326,6 +326,31 @@ TREX_API int trex_nk_generate_tree(const float* adjacency, int n_nodes, const ui
                           const uint8_t* draw_new_vals, const float* draw_u_accept, uint8_t* all_states, void* workspace,
                           void* stream);
 
+/* ---- file formats ----------------------------------------------------------------------
+ * The reference has no on-disk or wire format at all (its inputs exist only as in-memory arrays), so these replace
+ * nothing and have nothing to be parity-checked against; what they guarantee is the INPUT CONTRACT of the hot path
+ * (src/trex/sankoff.py:45-52, 60, 87-92; src/trex/utils/types.py:33).  Pure host code: every pointer is a HOST
+ * pointer, no CUDA call is made.
+ *
+ * FASTA / PHYLIP (sequential or interleaved, relaxed names) -> u8 states [taxon][site_stride]: index of the character
+ * in `alphabet` (case-insensitive, e.g. "ACGT" or "ARNDCQEGHILKMFPSTWYV"), 255 = no state (gap, ambiguity code,
+ * anything else; pad columns too).  Call once with states_host = names_host = NULL to get n_taxa / n_sites.
+ *   names_host: the taxon names, '\n'-separated and NUL-terminated (first word of each header), or NULL. */
+#define TREX_FORMAT_FASTA 0
+#define TREX_FORMAT_PHYLIP 1
+TREX_API int trex_parse_alignment_host(const char* text, size_t text_len, int format, const char* alphabet, int* n_taxa,
+                              int64_t* n_sites, uint8_t* states_host, int64_t site_stride, char* names_host,
+                              size_t names_capacity);
+/* Newick -> rooted BINARY tree in the node order run_dp requires: leaves 0..n-1 (row order of `taxon_names`, a
+ * '\n'-separated list as returned above, or order of appearance when NULL), internal nodes n..2n-2 in post-order —
+ * every child index is below its parent's, the root is the last node.  Branch lengths, comments and internal labels
+ * are ignored; unary nodes are transparent; a node with more than two children is an error (the reference's DP reads
+ * exactly two children, sankoff.py:60).
+ *   parent_host [2n-1] i32 (root: -1) or NULL; adjacency_host [2n-1][2n-1] f32 with adjacency[i][parent[i]] = 1 and
+ *   no root self-loop, or NULL; names_host: leaf names in leaf-index order, or NULL.  n_leaves is always written. */
+TREX_API int trex_parse_newick_host(const char* text, size_t text_len, const char* taxon_names, int* n_leaves,
+                           int32_t* parent_host, float* adjacency_host, char* names_host, size_t names_capacity);
+
 #ifdef __cplusplus
 }
 #endif

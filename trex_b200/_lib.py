@@ -60,6 +60,8 @@ SIGNATURES = {
   "trex_nk_generate_tree_workspace_bytes": (C.c_size_t, [_i, _i64]),
   "trex_nk_generate_tree": (_i, [_vp, _i, _vp, _i64, _i64, _i, _i, _vp, _vp, _f, _f, _f, _i, C.c_uint64, _vp, _vp, _vp, _vp,
                                  _vp, _vp, _vp, _vp, _vp]),
+  "trex_parse_alignment_host": (_i, [C.c_char_p, C.c_size_t, _i, C.c_char_p, _vp, _vp, _vp, _i64, _vp, C.c_size_t]),
+  "trex_parse_newick_host": (_i, [C.c_char_p, C.c_size_t, C.c_char_p, _vp, _vp, _vp, _vp, C.c_size_t]),
   "trex_fit_ancestors_workspace_bytes": (C.c_size_t, [_i, _i, _i64, _i]),
   "trex_fit_ancestors": (_i, [_vp, _vp, _i, _i, _i64, _i, _vp, _vp, _vp, _i, _f, _f, _i, _i64, _vp, _vp, _vp, _vp]),
 }
