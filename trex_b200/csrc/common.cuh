@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "../../include/trex_b200.h"
 
 namespace trex {
@@ -99,6 +101,29 @@ __device__ __forceinline__ void ld_f(const float* __restrict__ p, float (&out)[V
     float4 t = *reinterpret_cast<const float4*>(p);
     out[0] = t.x; out[1] = t.y; out[2] = t.z; out[3] = t.w;
   }
+}
+
+// row r of a [row][site] table whose rows are `row_bytes` apart: base + r * row_bytes as ONE 32x32->64 multiply-add
+// (IMAD.WIDE.U32) instead of the 64-bit multiply a `long long` stride costs (5-6 instructions per address).
+// Entry points check site_stride < 2^29, so a row pitch in bytes always fits 32 bits.
+template <typename T>
+__device__ __forceinline__ T* row_ptr(T* base, unsigned row_bytes, unsigned r) {
+  using B = typename std::conditional<std::is_const<T>::value, const char, char>::type;
+  return reinterpret_cast<T*>(reinterpret_cast<B*>(base) + (size_t)row_bytes * r);
+}
+
+// 2^x, one MUFU.EX2 (flush-to-zero: a term below 2^-126 of the largest one is nothing at float32)
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// log2(x), one MUFU.LG2, for x that is never subnormal (callers say why)
+__device__ __forceinline__ float lg2_ftz(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 
 // streaming read of data that is not re-read by this kernel (evict-first, bypass L1)

@@ -24,7 +24,7 @@ template <int AP>
 struct HardSmem {
   __align__(16) float C[AP * AP];            // [s][t], t >= A padded with 0
   __align__(16) float leaf_cost[(AP + 1) * AP];  // [o][s]
-  uint8_t leaf_arg[(AP + 1) * AP];
+  __align__(4) uint8_t leaf_arg[(AP + 1) * AP];
 };
 
 // min and first-argmin over t of crow[t] + d[t][v]
@@ -66,11 +66,12 @@ __device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long lo
                                           uint8_t* __restrict__ arg_out, bool is_root,
                                           float (&rmin)[V], const int (&o0)[V], const int (&o1)[V]) {
   float d0[L0 ? 1 : AP][V], d1[L1 ? 1 : AP][V];
+  const unsigned row_b = (unsigned)stride * 4u;  // bytes between two state rows of dp
   if constexpr (!L0) {
     const float* src = dp + (size_t)(c0 - n_leaves) * A * stride;
 #pragma unroll
     for (int t = 0; t < AP; ++t) {
-      if (t < A) ld_f<V>(src + (size_t)t * stride, d0[t]);
+      if (t < A) ld_f<V>(row_ptr(src, row_b, t), d0[t]);
       else {
 #pragma unroll
         for (int v = 0; v < V; ++v) d0[t][v] = INFINITY;
@@ -81,7 +82,7 @@ __device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long lo
     const float* src = dp + (size_t)(c1 - n_leaves) * A * stride;
 #pragma unroll
     for (int t = 0; t < AP; ++t) {
-      if (t < A) ld_f<V>(src + (size_t)t * stride, d1[t]);
+      if (t < A) ld_f<V>(row_ptr(src, row_b, t), d1[t]);
       else {
 #pragma unroll
         for (int v = 0; v < V; ++v) d1[t][v] = INFINITY;
@@ -134,8 +135,8 @@ __device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long lo
     }
 #pragma unroll
     for (int v = 0; v < V; ++v) o[v] = b0[v] + b1[v];  // (0 + cost0) + cost1, sankoff.py:70
-    st_f<V>(out + (size_t)s * stride, o);
-    if (arg_out) st_arg_pair<V>(arg_out + (size_t)s * 2 * stride, i0, i1, true);
+    st_f<V>(row_ptr(out, row_b, s), o);
+    if (arg_out) st_arg_pair<V>(row_ptr(arg_out, row_b >> 1, s), i0, i1, true);
     if (is_root) {
 #pragma unroll
       for (int v = 0; v < V; ++v) rmin[v] = fminf(rmin[v], o[v]);
@@ -143,8 +144,49 @@ __device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long lo
   }
 }
 
+// A node whose two children are leaves ("cherry", half of the internal nodes of a balanced tree): both rows come from the
+// leaf lookup table, whole table rows at a time (LDS.128 for the scores, one word per 4 back-pointers) instead of one
+// LDS + one LDS.U8 with its own address per (child, site, state) — 850 -> ~250 instructions per node and lane.
+template <int AP, int V>
+__device__ __forceinline__ void hard_cherry(const HardSmem<AP>& sm, int A, unsigned row_b, float* __restrict__ out,
+                                            uint8_t* __restrict__ arg_out, const int (&o0)[V], const int (&o1)[V]) {
+  static_assert(AP % 4 == 0, "hard_cherry: whole float4 table rows");
+  float c0[V][AP], c1[V][AP];
+  unsigned a0[V][AP / 4], a1[V][AP / 4];
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+#pragma unroll
+    for (int j = 0; j < AP / 4; ++j) {
+      const float4 x = *reinterpret_cast<const float4*>(&sm.leaf_cost[o0[v] * AP + 4 * j]);
+      const float4 y = *reinterpret_cast<const float4*>(&sm.leaf_cost[o1[v] * AP + 4 * j]);
+      c0[v][4 * j] = x.x; c0[v][4 * j + 1] = x.y; c0[v][4 * j + 2] = x.z; c0[v][4 * j + 3] = x.w;
+      c1[v][4 * j] = y.x; c1[v][4 * j + 1] = y.y; c1[v][4 * j + 2] = y.z; c1[v][4 * j + 3] = y.w;
+      a0[v][j] = *reinterpret_cast<const unsigned*>(&sm.leaf_arg[o0[v] * AP + 4 * j]);
+      a1[v][j] = *reinterpret_cast<const unsigned*>(&sm.leaf_arg[o1[v] * AP + 4 * j]);
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < AP; ++s) {
+    if (s < A) {
+      float o[V];
+#pragma unroll
+      for (int v = 0; v < V; ++v) o[v] = c0[v][s] + c1[v][s];  // (0 + cost0) + cost1, sankoff.py:70
+      st_f<V>(row_ptr(out, row_b, s), o);
+      if (arg_out) {
+        int i0[V], i1[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          i0[v] = (a0[v][s / 4] >> (8 * (s % 4))) & 0xff;
+          i1[v] = (a1[v][s / 4] >> (8 * (s % 4))) & 0xff;
+        }
+        st_arg_pair<V>(row_ptr(arg_out, row_b >> 1, s), i0, i1, true);
+      }
+    }
+  }
+}
+
 template <int AP, int V, int THREADS>
-__global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p) {
+__global__ void __launch_bounds__(THREADS, 4) hard_fwd_kernel(const HardFwdParams p) {
   __shared__ HardSmem<AP> sm;
   const int A = p.n_states;
   const int tid = threadIdx.x;
@@ -189,6 +231,33 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
 #pragma unroll
   for (int v = 0; v < V; ++v) rmin[v] = INFINITY;
 
+  // The top part consumes rows the subtree segments wrote (another launch): a stateless leaf anywhere below disables
+  // the packed-key path exactly as in the single walk.  One look at all leaves of this CTA's sites, 16 bytes per load,
+  // the whole CTA sharing the verdict (coarser than the per-site flag of the single walk; both paths give the same
+  // rows while the keys are exact, so only speed depends on it).
+  bool cta_bad = false;
+  if (p.phase == 2 && fast_ok) {
+    constexpr int kChunks = THREADS * V / 16;  // 16-byte chunks per leaf row of this CTA's site range
+    static_assert(THREADS % kChunks == 0, "leaf scan: threads per row");
+    const long long off = (long long)blockIdx.x * THREADS * V + (tid % kChunks) * 16;
+    unsigned any = 0;
+    if (off < p.n_sites) {
+      const unsigned lim = (unsigned)A * 0x01010101u;
+      if ((reinterpret_cast<uintptr_t>(p.leaf) & 15) == 0) {
+        const uint8_t* q = p.leaf + off;
+#pragma unroll 4
+        for (int c = tid / kChunks; c < p.n_leaves; c += THREADS / kChunks) {
+          const uint4 w = __ldg(reinterpret_cast<const uint4*>(row_ptr(q, (unsigned)p.stride, c)));
+          any |= __vcmpgeu4(w.x, lim) | __vcmpgeu4(w.y, lim) | __vcmpgeu4(w.z, lim) | __vcmpgeu4(w.w, lim);
+        }
+      } else {  // a leaf table that is not 16-byte aligned: bytes
+        for (int c = tid / kChunks; c < p.n_leaves; c += THREADS / kChunks)
+          for (int j = 0; j < 16; ++j) any |= p.leaf[(size_t)c * p.stride + off + j] >= A;
+      }
+    }
+    cta_bad = __syncthreads_or(any != 0);
+  }
+
   if (active) {
     float* dp = p.dp + (size_t)tree * n_int * A * p.stride + site0;
     uint8_t* arg = p.arg ? p.arg + ((size_t)tree * n_int * A * p.stride + site0) * 2 : nullptr;
@@ -197,17 +266,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
     const int32_t* order = wk.ord;
     const int32_t* ch0 = plan.child(0);
     const int32_t* ch1 = plan.child(1);
-    bool bad = false;  // an out-of-range leaf state puts ~1e5 values into internal rows
-    if (p.phase == 2 && fast_ok) {
-      // the top part consumes rows of the subtree segments (another launch): a stateless leaf anywhere below
-      // disables the packed-key path exactly as in the single walk, so look at all leaves of these sites
-      for (int c = 0; c < p.n_leaves; ++c) {
-        int o[V];
-        ld_u8<V>(leaf + (size_t)c * p.stride, o);
-#pragma unroll
-        for (int v = 0; v < V; ++v) bad = bad || o[v] >= A;
-      }
-    }
+    bool bad = cta_bad;  // an out-of-range leaf state puts ~1e5 values into internal rows
     for (int i = 0; i < wk.n_fwd; ++i) {
       const int node = __ldg(order + i);
       const int k = node - p.n_leaves;
@@ -232,7 +291,12 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_kernel(const HardFwdParams p
 #define TREX_NODE(L0, L1, F) \
   hard_node<AP, V, L0, L1, F>(sm, A, p.stride, dp, leaf, p.n_leaves, c0, c1, out, aout, is_root, rmin, o0, o1)
       if (l0 && l1) {
-        TREX_NODE(true, true, false);
+        if constexpr (AP % 4 == 0) {
+          if (!is_root) hard_cherry<AP, V>(sm, A, (unsigned)p.stride * 4u, out, aout, o0, o1);
+          else TREX_NODE(true, true, false);
+        } else {
+          TREX_NODE(true, true, false);
+        }
       } else if (fast_ok && !bad) {
         if (l0) TREX_NODE(true, false, true);
         else if (l1) TREX_NODE(false, true, true);
@@ -287,8 +351,8 @@ extern "C" int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leave
   TREX_CHECK_ARG(plan && leaf_states && cost && dp, "trex_sankoff_hard_fwd: null pointer");
   TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves, "trex_sankoff_hard_fwd: need n_all > n_leaves >= 1");
   TREX_CHECK_ARG(n_states >= 1 && n_states <= 32, "trex_sankoff_hard_fwd: n_states %d not in 1..32", n_states);
-  TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0,
-                 "trex_sankoff_hard_fwd: site_stride must be a multiple of 16 and >= n_sites");
+  TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0 && site_stride < (1LL << 29),
+                 "trex_sankoff_hard_fwd: site_stride must be a multiple of 16, >= n_sites and < 2^29");
   TREX_CHECK_ARG(batch >= 1 && batch <= 65535, "trex_sankoff_hard_fwd: batch out of range");
   TREX_CHECK_ARG(mode == TREX_MODE_AUTO || mode == TREX_MODE_GENERAL, "trex_sankoff_hard_fwd: bad mode");
   cudaStream_t s = (cudaStream_t)stream;

@@ -27,7 +27,7 @@ __device__ __forceinline__ void load_row(const float* __restrict__ src, int A, l
                                          float (&d)[AP][V]) {
 #pragma unroll
   for (int t = 0; t < AP; ++t) {
-    if (t < A) ld_f<V>(src + (size_t)t * stride, d[t]);
+    if (t < A) ld_f<V>(row_ptr(src, (unsigned)stride * 4u, t), d[t]);
     else {
 #pragma unroll
       for (int v = 0; v < V; ++v) d[t][v] = INFINITY;
@@ -45,7 +45,7 @@ __device__ __forceinline__ void to_exp_domain(float (&d)[AP][V], float (&m)[V], 
     for (int t = 1; t < AP; ++t) mm = fminf(mm, d[t][v]);
     m[v] = mm;
 #pragma unroll
-    for (int t = 0; t < AP; ++t) d[t][v] = exp2f((mm - d[t][v]) * c1);
+    for (int t = 0; t < AP; ++t) d[t][v] = ex2_ftz((mm - d[t][v]) * c1);
   }
 }
 
@@ -88,15 +88,15 @@ __device__ __forceinline__ void soft_node(const SoftFwdSmem<AP>& sm, int A, long
         float z = 0.f;
 #pragma unroll
         for (int t = 0; t < AP; ++t) z = fmaf(row[t], d0[t][v], z);
-        a = fmaf(-tln2, __log2f(z), m0[v]);
+        a = fmaf(-tln2, lg2_ftz(z), m0[v]);  // z >= exp(-80): the term of the smallest row entry (c_ok), not subnormal
       } else {
         float mm = INFINITY;
 #pragma unroll
         for (int t = 0; t < AP; ++t) mm = fminf(mm, row[t] + d0[t][v]);
         float z = 0.f;
 #pragma unroll
-        for (int t = 0; t < AP; ++t) z += exp2f((mm - (row[t] + d0[t][v])) * c1);
-        a = fmaf(-tln2, __log2f(z), mm);
+        for (int t = 0; t < AP; ++t) z += ex2_ftz((mm - (row[t] + d0[t][v])) * c1);
+        a = fmaf(-tln2, lg2_ftz(z), mm);  // z >= 1: the minimum's own term
       }
       if constexpr (!R1) {
         b = sm.leaf_soft[o1[v] * AP + s];
@@ -104,24 +104,24 @@ __device__ __forceinline__ void soft_node(const SoftFwdSmem<AP>& sm, int A, long
         float z = 0.f;
 #pragma unroll
         for (int t = 0; t < AP; ++t) z = fmaf(row[t], d1[t][v], z);
-        b = fmaf(-tln2, __log2f(z), m1[v]);
+        b = fmaf(-tln2, lg2_ftz(z), m1[v]);
       } else {
         float mm = INFINITY;
 #pragma unroll
         for (int t = 0; t < AP; ++t) mm = fminf(mm, row[t] + d1[t][v]);
         float z = 0.f;
 #pragma unroll
-        for (int t = 0; t < AP; ++t) z += exp2f((mm - (row[t] + d1[t][v])) * c1);
-        b = fmaf(-tln2, __log2f(z), mm);
+        for (int t = 0; t < AP; ++t) z += ex2_ftz((mm - (row[t] + d1[t][v])) * c1);
+        b = fmaf(-tln2, lg2_ftz(z), mm);
       }
       o[v] = a + b;
     }
-    st_f<V>(out + (size_t)s * stride, o);
+    st_f<V>(row_ptr(out, (unsigned)stride * 4u, s), o);
   }
 }
 
 template <int AP, int V, int THREADS>
-__global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p) {
+__global__ void __launch_bounds__(THREADS, 4) soft_fwd_kernel(const SoftFwdParams p) {
   __shared__ SoftFwdSmem<AP> sm;
   const int A = p.n_states;
   const int tid = threadIdx.x;
@@ -226,8 +226,8 @@ __global__ void __launch_bounds__(THREADS) soft_fwd_kernel(const SoftFwdParams p
       for (int s = 1; s < AP; ++s) mm = fminf(mm, x[s][v]);
       float z = 0.f;
 #pragma unroll
-      for (int s = 0; s < AP; ++s) z += exp2f((mm - x[s][v]) * c1);
-      if (site0 + v < p.n_sites) acc += (double)fmaf(-tln2, __log2f(z), mm);
+      for (int s = 0; s < AP; ++s) z += ex2_ftz((mm - x[s][v]) * c1);
+      if (site0 + v < p.n_sites) acc += (double)fmaf(-tln2, lg2_ftz(z), mm);
     }
     }
   }
@@ -266,8 +266,8 @@ extern "C" int trex_sankoff_soft_fwd(const int32_t* plan, int n_all, int n_leave
                  "trex_sankoff_soft_fwd: exactly one of leaf_states / leaf_cost must be given");
   TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves, "trex_sankoff_soft_fwd: need n_all > n_leaves >= 1");
   TREX_CHECK_ARG(n_states >= 1 && n_states <= 32, "trex_sankoff_soft_fwd: n_states %d not in 1..32", n_states);
-  TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0,
-                 "trex_sankoff_soft_fwd: site_stride must be a multiple of 16 and >= n_sites");
+  TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0 && site_stride < (1LL << 29),
+                 "trex_sankoff_soft_fwd: site_stride must be a multiple of 16, >= n_sites and < 2^29");
   TREX_CHECK_ARG(batch >= 1 && batch <= 65535, "trex_sankoff_soft_fwd: batch out of range");
   TREX_CHECK_ARG(temperature > 0.f && temperature < 1e30f, "trex_sankoff_soft_fwd: temperature must be > 0");
   cudaStream_t s = (cudaStream_t)stream;
