@@ -59,12 +59,16 @@ __device__ __forceinline__ void minplus(const float (&crow)[AP], const float (&d
   }
 }
 
-template <int AP, int V, bool L0, bool L1, bool FAST>
-__device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long long stride,
+// FA: n_states == AP (no padded states: 4, 8, ..., 20, ...) — the state count becomes a compile-time constant, so the row
+// loads lose their predicates and INFINITY defaults (170 of the 440 instructions of a node's load phase) and the
+// state loop its remainder handling.
+template <int AP, int V, bool L0, bool L1, bool FAST, bool FA>
+__device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A_rt, long long stride,
                                           const float* __restrict__ dp, const uint8_t* __restrict__ leaf,
                                           int n_leaves, int c0, int c1, float* __restrict__ out,
                                           uint8_t* __restrict__ arg_out, bool is_root,
                                           float (&rmin)[V], const int (&o0)[V], const int (&o1)[V]) {
+  const int A = FA ? AP : A_rt;
   float d0[L0 ? 1 : AP][V], d1[L1 ? 1 : AP][V];
   const unsigned row_b = (unsigned)stride * 4u;  // bytes between two state rows of dp
   if constexpr (!L0) {
@@ -147,10 +151,11 @@ __device__ __forceinline__ void hard_node(const HardSmem<AP>& sm, int A, long lo
 // A node whose two children are leaves ("cherry", half of the internal nodes of a balanced tree): both rows come from the
 // leaf lookup table, whole table rows at a time (LDS.128 for the scores, one word per 4 back-pointers) instead of one
 // LDS + one LDS.U8 with its own address per (child, site, state) — 850 -> ~250 instructions per node and lane.
-template <int AP, int V>
-__device__ __forceinline__ void hard_cherry(const HardSmem<AP>& sm, int A, unsigned row_b, float* __restrict__ out,
+template <int AP, int V, bool FA>
+__device__ __forceinline__ void hard_cherry(const HardSmem<AP>& sm, int A_rt, unsigned row_b, float* __restrict__ out,
                                             uint8_t* __restrict__ arg_out, const int (&o0)[V], const int (&o1)[V]) {
   static_assert(AP % 4 == 0, "hard_cherry: whole float4 table rows");
+  const int A = FA ? AP : A_rt;
   float c0[V][AP], c1[V][AP];
   unsigned a0[V][AP / 4], a1[V][AP / 4];
 #pragma unroll
@@ -173,13 +178,20 @@ __device__ __forceinline__ void hard_cherry(const HardSmem<AP>& sm, int A, unsig
       for (int v = 0; v < V; ++v) o[v] = c0[v][s] + c1[v][s];  // (0 + cost0) + cost1, sankoff.py:70
       st_f<V>(row_ptr(out, row_b, s), o);
       if (arg_out) {
-        int i0[V], i1[V];
+        if constexpr (V == 2) {  // bytes [slot0, slot1] of site 0, then of site 1: three PRMTs
+          const unsigned sel = (s % 4) | ((4 + s % 4) << 4);
+          const unsigned lo = __byte_perm(a0[0][s / 4], a1[0][s / 4], sel);
+          const unsigned hi = __byte_perm(a0[1][s / 4], a1[1][s / 4], sel);
+          __stcs(reinterpret_cast<unsigned*>(row_ptr(arg_out, row_b >> 1, s)), __byte_perm(lo, hi, 0x5410u));
+        } else {
+          int i0[V], i1[V];
 #pragma unroll
-        for (int v = 0; v < V; ++v) {
-          i0[v] = (a0[v][s / 4] >> (8 * (s % 4))) & 0xff;
-          i1[v] = (a1[v][s / 4] >> (8 * (s % 4))) & 0xff;
+          for (int v = 0; v < V; ++v) {
+            i0[v] = (a0[v][s / 4] >> (8 * (s % 4))) & 0xff;
+            i1[v] = (a1[v][s / 4] >> (8 * (s % 4))) & 0xff;
+          }
+          st_arg_pair<V>(row_ptr(arg_out, row_b >> 1, s), i0, i1, true);
         }
-        st_arg_pair<V>(row_ptr(arg_out, row_b >> 1, s), i0, i1, true);
       }
     }
   }
@@ -288,12 +300,18 @@ __global__ void __launch_bounds__(THREADS, 4) hard_fwd_kernel(const HardFwdParam
       float* out = dp + (size_t)k * A * p.stride;
       uint8_t* aout = arg ? arg + (size_t)k * 2 * A * p.stride : nullptr;
       const bool is_root = node == p.n_all - 1;
-#define TREX_NODE(L0, L1, F) \
-  hard_node<AP, V, L0, L1, F>(sm, A, p.stride, dp, leaf, p.n_leaves, c0, c1, out, aout, is_root, rmin, o0, o1)
+#define TREX_NODE(L0, L1, F)                                                                                          \
+  do {                                                                                                                \
+    if (A == AP)                                                                                                      \
+      hard_node<AP, V, L0, L1, F, true>(sm, A, p.stride, dp, leaf, p.n_leaves, c0, c1, out, aout, is_root, rmin, o0, o1);  \
+    else                                                                                                              \
+      hard_node<AP, V, L0, L1, F, false>(sm, A, p.stride, dp, leaf, p.n_leaves, c0, c1, out, aout, is_root, rmin, o0, o1); \
+  } while (0)
       if (l0 && l1) {
         if constexpr (AP % 4 == 0) {
-          if (!is_root) hard_cherry<AP, V>(sm, A, (unsigned)p.stride * 4u, out, aout, o0, o1);
-          else TREX_NODE(true, true, false);
+          if (is_root) TREX_NODE(true, true, false);
+          else if (A == AP) hard_cherry<AP, V, true>(sm, A, (unsigned)p.stride * 4u, out, aout, o0, o1);
+          else hard_cherry<AP, V, false>(sm, A, (unsigned)p.stride * 4u, out, aout, o0, o1);
         } else {
           TREX_NODE(true, true, false);
         }

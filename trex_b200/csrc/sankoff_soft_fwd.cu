@@ -49,11 +49,13 @@ __device__ __forceinline__ void to_exp_domain(float (&d)[AP][V], float (&m)[V], 
   }
 }
 
-template <int AP, int V, bool R0, bool R1, bool EXPDOM>
-__device__ __forceinline__ void soft_node(const SoftFwdSmem<AP>& sm, int A, long long stride,
+// FA: n_states == AP, the state count is a compile-time constant (no load predicates, no loop remainder)
+template <int AP, int V, bool R0, bool R1, bool EXPDOM, bool FA>
+__device__ __forceinline__ void soft_node(const SoftFwdSmem<AP>& sm, int A_rt, long long stride,
                                           const float* __restrict__ src0, const float* __restrict__ src1,
                                           const int (&o0)[V], const int (&o1)[V], float c1, float tln2,
                                           float* __restrict__ out) {
+  const int A = FA ? AP : A_rt;
   float d0[R0 ? AP : 1][V], d1[R1 ? AP : 1][V];
   float m0[V], m1[V];
   if constexpr (R0) load_row<AP, V>(src0, A, stride, d0);
@@ -200,8 +202,11 @@ __global__ void __launch_bounds__(THREADS, 4) soft_fwd_kernel(const SoftFwdParam
         }
       }
       float* out = dp + (size_t)k * A * p.stride;
-#define TREX_SNODE(R0, R1, E) \
-  soft_node<AP, V, R0, R1, E>(sm, A, p.stride, src0, src1, o0, o1, c1, tln2, out)
+#define TREX_SNODE(R0, R1, E)                                                                       \
+  do {                                                                                              \
+    if (A == AP) soft_node<AP, V, R0, R1, E, true>(sm, A, p.stride, src0, src1, o0, o1, c1, tln2, out);  \
+    else soft_node<AP, V, R0, R1, E, false>(sm, A, p.stride, src0, src1, o0, o1, c1, tln2, out);         \
+  } while (0)
       if (expdom) {
         if (src0 && src1) TREX_SNODE(true, true, true);
         else if (src0) TREX_SNODE(true, false, true);
