@@ -51,11 +51,13 @@ def measured_peaks():
   return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback (B200_PROFILING.md)"
 
 
-def alg_bytes_per_site(n, A):
-  """SURVEY §8(d) algorithmic (compulsory) bytes per site and tree, per pass."""
+def alg_bytes_per_site(n, A, words=False):
+  """SURVEY §8(d) algorithmic (compulsory) bytes per site and tree, per pass.  ``words``: the back-pointers are pointer
+  words (TREX_MODE_COMPACT_ARG, uniform cost: 8 bytes per node and site, all of them read by the traceback) instead
+  of the byte table (2A bytes per node and site written, 2 of them read)."""
   return {
-    "hard_fwd": n + (2 * n - 3) * 4 * A + (n - 1) * 2 * A,
-    "hard_bwd": 3 * (n - 1) + 1,
+    "hard_fwd": n + (2 * n - 3) * 4 * A + (n - 1) * (8 if words else 2 * A),
+    "hard_bwd": ((8 if words else 2) + 1) * (n - 1) + 1,
     "soft_fwd": n + (2 * n - 3) * 4 * A,
     "soft_bwd": n + (4 * n - 5) * 4 * A,
   }
@@ -882,7 +884,7 @@ def run_gpu(args):
   if rank == 0:
     pk, peak_src = measured_peaks()
     peak = float(pk["hbm_gbs"])
-    per_site = alg_bytes_per_site(n, A)
+    per_site = alg_bytes_per_site(n, A, words=True)  # c5 says unit cost: the engine writes pointer words
     traffic_tab = ncu_traffic() if L == N_SITES else {}
     roof_all = {}
     for nm in ["hard_fwd", "hard_bwd", "soft_fwd", "soft_bwd"]:

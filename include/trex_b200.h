@@ -44,6 +44,18 @@ extern "C" {
 /* inner-loop selection of the hard Sankoff forward (testing knob; AUTO is the product path) */
 #define TREX_MODE_AUTO 0    /* packed-key path when the cost matrix allows it, else exact-f32 */
 #define TREX_MODE_GENERAL 1 /* always the exact-f32 compare/select path */
+/* OR-ed into `mode` of trex_sankoff_hard_fwd: when the cost matrix is uniform (C[s][s] = 0, C[s][t] = a: the O(A)
+ * kernels run) and 4 <= n_states <= 20, the back-pointers of a node are written as two POINTER WORDS per site —
+ *   word of slot c (c = 0: first child): bits 0-4 = that child's first-minimum state j, bit 5+s = "parent state s
+ *   keeps its own state", i.e. pointer(s) = bit ? s : j —
+ * into state rows 0-3 of the node's [n_states][site][2] byte table (row r, site i: bits 16r..16r+15 of
+ * word0 | word1 << 32, little-endian; rows 4.. are not written).  8 bytes per (node, site) instead of 2 * n_states,
+ * coalesced on both sides; buffer size, alignment and every offset (tree batches, site blocks) stay those of the byte
+ * table.  For any other cost matrix or state count the byte table is written as without the flag.  Only
+ * trex_sankoff_traceback_cost — which is given the same cost matrix and mode and repeats the device-side decision —
+ * can read the result; trex_sankoff_traceback and trex_sankoff_export_bt need a table written WITHOUT this flag.
+ * No counterpart in the reference (its backtracking table is (n_all, A, 4) f32 per site, sankoff.py:80-83). */
+#define TREX_MODE_COMPACT_ARG 0x100
 
 /* plan status bits (word 3 of each tree's plan header) */
 #define TREX_PLAN_HAS_SENTINEL_CHILD 1 /* some node has < 2 children, or a child id >= its own */
@@ -110,6 +122,15 @@ TREX_API int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves
                            int64_t n_sites, int64_t site_stride, int batch,
                            const uint8_t* leaf_states, const float* dp, const uint8_t* argmin,
                            uint8_t* anc_states, unsigned long long* edge_hist, void* stream);
+/* The same for an `argmin` buffer written by trex_sankoff_hard_fwd(..., cost, ..., mode): `cost` [A][A] f32 and `mode`
+ * must be the ones of that call (mode may carry TREX_MODE_COMPACT_ARG; without the flag this is
+ * trex_sankoff_traceback).  The kernel repeats the forward's device-side test of the cost matrix to know whether it
+ * reads pointer words or the byte table. */
+TREX_API int trex_sankoff_traceback_cost(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                                int64_t n_sites, int64_t site_stride, int batch,
+                                const uint8_t* leaf_states, const float* cost, int mode, const float* dp,
+                                const uint8_t* argmin, uint8_t* anc_states, unsigned long long* edge_hist,
+                                void* stream);
 
 /* ---- exports to the reference's layouts (what run_sankoff returns, sankoff.py:161-188) ------
  *   dp_ref    [L][n_all][A] f32 incl. the explicit leaf rows (1e5 / 0)

@@ -131,7 +131,8 @@ def test_back_pointers_bit_exact_on_the_1024_leaf_tree(cost_kind, seg):
     eng = SankoffEngine(2 * n - 1, n, A, L)
     eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states))
     eng.hard_forward(torch.from_numpy(cost), want_argmin=True)
-    arg = eng.argmin[0, :, :, :L, :].permute(2, 0, 3, 1).cpu().numpy()  # (L, n_int, slot, A)
+    assert eng.wrote_pointer_words() == (cost_kind == "unit")
+    arg = eng.argmin_table()[0, :, :, :L, :].permute(2, 0, 3, 1).cpu().numpy()  # (L, n_int, slot, A)
     assert np.array_equal(arg, tabs["argmin"][:, n:].astype(np.uint8))
     assert np.array_equal(eng.export_dp().cpu().numpy(), tabs["dp"])
     eng.traceback()

@@ -39,7 +39,7 @@ def _case(kind, n, A, L, seed, cost_kind="unit", rate=0.2):
 def _native_tables(eng, tree=0):
   """dp (L,n_all,A), argmin (L,n_int,2,A) in the oracle's layout."""
   dp = eng.export_dp(tree).cpu().numpy()
-  arg = eng.argmin[tree, :, :, : eng.L, :].permute(2, 0, 3, 1).cpu().numpy()  # (L, n_int, slot, A)
+  arg = eng.argmin_table()[tree, :, :, : eng.L, :].permute(2, 0, 3, 1).cpu().numpy()  # (L, n_int, slot, A)
   return dp, arg
 
 
@@ -223,10 +223,11 @@ def test_full_size_properties(n, A, L):
   eng.set_adjacency(torch.from_numpy(adj)).set_leaf_states_u8(torch.from_numpy(states[:n]))
   eng.hard_forward(torch.from_numpy(cost), mode=0)
   dp_fast = eng.dp.clone()
-  arg_fast = eng.argmin.clone()
+  arg_fast = eng.argmin_table().clone()
   rm = eng.root_min[0, :L].cpu().numpy()
   eng.hard_forward(torch.from_numpy(cost), mode=1)
   assert torch.equal(dp_fast[..., :L], eng.dp[..., :L])
+  assert not eng.wrote_pointer_words()  # mode=1: the byte table, whatever the matrix
   assert torch.equal(arg_fast[..., :L, :], eng.argmin[..., :L, :])
   fitch = so.fitch_score(adj, states[:n], n_all, A, n)
   assert np.array_equal(rm.astype(np.int64), fitch)
@@ -385,3 +386,40 @@ def test_stateless_leaves_take_the_exact_back_pointer_path(A, ck):
   eng.traceback()
   want = so.traceback_topdown(tabs, n_all, n)
   assert np.array_equal(eng.anc[0, :, :L].cpu().numpy(), want[n:].astype(np.uint8))
+
+
+@pytest.mark.parametrize("seg", [0, 1])
+@pytest.mark.parametrize("kind,n,A,L,ck,words", [
+  ("balanced", 64, 20, 700, "unit", True), ("random", 37, 4, 333, "unit3", True), ("cat", 20, 5, 129, "unit", True),
+  ("random", 50, 20, 400, "int", False),    # not uniform: the byte table, whatever the flag says
+  ("random", 21, 3, 100, "unit", False),    # 3 states: 8 bytes of words would not fit the 6 bytes of table
+  ("random", 21, 24, 100, "unit", False)])  # 24 states run in the 32-wide tile: no words
+def test_pointer_words_and_byte_table_are_the_same_back_pointers(kind, n, A, L, ck, words, seg, monkeypatch):
+  """TREX_MODE_COMPACT_ARG (include/trex_b200.h): the decoded words equal the byte table for EVERY parent state
+  (= the oracle's argmin, sankoff.py:80-83), and the traceback is the same from either form; batch of two trees."""
+  torch = _torch()
+  from trex_b200.sankoff import SankoffEngine
+
+  monkeypatch.setenv("TREX_SEGMENTS", str(seg))
+  adj, cost, states, _ = _case(kind, n, A, L, seed=n * 7 + A, cost_kind=ck)
+  adj2, _, _, _ = _case("random", n, A, L, seed=n * 7 + A + 1, cost_kind=ck)
+  states[1, ::17] = 255                                        # stateless leaf sites
+  n_all = 2 * n - 1
+  both = torch.from_numpy(np.stack([adj, adj2]))
+  out = {}
+  for compact in (False, True):
+    eng = SankoffEngine(n_all, n, A, L, batch=2)
+    eng.set_adjacency(both).set_leaf_states_u8(torch.from_numpy(states[:n]))
+    eng.argmin.fill_(0xEE)                                      # rows the words do not cover must not matter
+    eng.hard_forward(torch.from_numpy(cost), want_argmin=True, compact_arg=compact)
+    assert eng.wrote_pointer_words() == (compact and words)
+    table = eng.argmin_table()[..., :L, :].cpu().numpy()
+    eng.traceback(want_hist=True)
+    out[compact] = (table, eng.anc[..., :L].cpu().numpy(), eng.edge_hist.cpu().numpy(), eng.dp[..., :L].cpu().numpy())
+  for a, b in zip(out[False], out[True]):
+    assert np.array_equal(a, b)
+  for t, ad in enumerate((adj, adj2)):
+    tabs = so.run_sankoff_tables(ad, cost, states[:n], n_all, A, n)
+    want = np.transpose(tabs["argmin"][:, n:].astype(np.uint8), (1, 3, 0, 2))  # (L, n_int, slot, A) -> (n_int, A, L, slot)
+    assert np.array_equal(out[True][0][t], want)
+    assert np.array_equal(out[True][1][t], so.traceback_topdown(tabs, n_all, n)[n:].astype(np.uint8))

@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("TREX_B200_LIB") or os.path.join(_HERE, "libtrex_b200.
 
 MODE_AUTO = 0
 MODE_GENERAL = 1
+MODE_COMPACT_ARG = 0x100  # OR-ed into mode: pointer words instead of the byte table when the cost is uniform
 PLAN_HAS_SENTINEL_CHILD = 1
 PLAN_NOT_A_TREE = 2
 PLAN_SHARED_LEAF = 4
@@ -32,6 +33,7 @@ SIGNATURES = {
   "trex_encode_leaf_states": (_i, [_vp, _i, _i64, _i64, _i, _vp, _i64, _vp]),
   "trex_sankoff_hard_fwd": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
   "trex_sankoff_traceback": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
+  "trex_sankoff_traceback_cost": (_i, [_vp, _i, _i, _i, _i64, _i64, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp]),
   "trex_sankoff_export_dp": (_i, [_i, _i, _i, _i64, _i64, _vp, _vp, _vp, _vp]),
   "trex_sankoff_export_recon": (_i, [_i, _i, _i64, _i64, _vp, _i64, _vp, _vp, _vp, _vp]),
   "trex_sankoff_export_bt": (_i, [_vp, _i, _i, _i, _i64, _i64, _vp, _vp, _vp]),

@@ -18,7 +18,13 @@ struct HardFwdParams {
   double* total;
   int mode;
   int phase;  // node list of this launch (common.cuh: Walk): 0 whole tree, 1 segment blockIdx.z, 2 top part
+  int compact;  // TREX_MODE_COMPACT_ARG asked for and compact_arg_ok(n_states): the uniform kernel writes pointer words
 };
+
+// Pointer words (sankoff_uniform.cu) need 5 + n_states bits of a 32-bit word and, living at the start of the byte
+// table's buffer, 8 bytes per (node, site) of its 2 * n_states: 4 <= n_states <= 20 (the 20-state tile is the widest
+// one below 27).
+__host__ __device__ inline bool compact_arg_ok(int n_states) { return n_states >= 4 && n_states <= 20; }
 
 struct SoftFwdParams {
   const int32_t* plan;
@@ -57,9 +63,13 @@ __device__ __forceinline__ bool fast_cost_ok(float c, int n_all) {
 }
 
 // true (CTA-wide) when the O(A) kernels of sankoff_uniform.cu own this call
+__device__ __forceinline__ bool hard_uniform_applies(const float* __restrict__ cost, int n_states, int mode, int n_all,
+                                                     float& a) {
+  const bool uni = cost_is_uniform(cost, n_states, a);
+  return uni && mode == TREX_MODE_AUTO && fast_cost_ok(a, n_all);
+}
 __device__ __forceinline__ bool hard_uniform_applies(const HardFwdParams& p, float& a) {
-  const bool uni = cost_is_uniform(p.cost, p.n_states, a);
-  return uni && p.mode == TREX_MODE_AUTO && fast_cost_ok(a, p.n_all);
+  return hard_uniform_applies(p.cost, p.n_states, p.mode, p.n_all, a);
 }
 __device__ __forceinline__ bool soft_uniform_applies(const SoftFwdParams& p, float& a) {
   const bool uni = cost_is_uniform(p.cost, p.n_states, a);

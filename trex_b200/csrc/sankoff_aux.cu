@@ -1,6 +1,10 @@
 // Hard-Sankoff companions: leaf encoding, ancestral-state traceback (+ edge histogram) and
 // the exports from the native site-contiguous tables to the reference's array layouts.
+#include <cstdlib>
+#include <type_traits>
+
 #include "common.cuh"
+#include "fwd_params.cuh"
 
 namespace trex {
 
@@ -34,6 +38,10 @@ struct TraceParams {
   uint8_t* anc;
   unsigned long long* hist;
   int phase;  // node list of this launch (common.cuh: Walk): 0 whole tree, 1 segment blockIdx.z, 2 top part
+  // trex_sankoff_traceback_cost: the forward's cost matrix and mode, to repeat its choice of table format
+  const float* cost;
+  int mode;
+  int compact;  // the forward was asked for pointer words (TREX_MODE_COMPACT_ARG) and n_states allows them
 };
 
 template <int V, int THREADS>
@@ -44,6 +52,12 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
   const int n_int = p.n_all - p.n_leaves;
   PlanView plan(p.plan + (size_t)tree * p.plan_words, n_int);
   if (p.phase == 1 && (int)blockIdx.z >= plan.hdr()[2]) return;  // empty segment slice (CTA-uniform)
+  // pointer words (sankoff_uniform.cu) or the byte table: the test the forward kernels made, on the same matrix
+  bool words = false;
+  if (p.compact) {
+    float a_uni;
+    words = hard_uniform_applies(p.cost, A, p.mode, p.n_all, a_uni);
+  }
   if (p.hist) {
     for (int i = threadIdx.x; i < A * A; i += THREADS) s_hist[i] = 0;
     __syncthreads();
@@ -94,9 +108,36 @@ __global__ void __launch_bounds__(THREADS) traceback_kernel(const TraceParams p)
 #pragma unroll
       for (int v = 0; v < V; ++v) pair[v] = 0;
       if (ch0 >= p.n_leaves || ch1 >= p.n_leaves) {
+        if (words) {  // rows 0-3 of the node's table: the 16-bit quarters of (word of slot 0, word of slot 1), coalesced
+                      // and the same for every parent state; pointer(s) = bit 5+s ? s : bits 0-4.  (Requesting the next
+                      // node's words a node ahead and handing the child's state over in registers was tried: slower,
+                      // 0.36 vs 0.34 ms — the walk is bound by instructions, not by the latency of its reads.)
+          unsigned q[4][V];  // one access per row: the V 16-bit quarters of this lane's sites
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const uint8_t* src = arg + ((size_t)k * A + r) * p.stride * 2;
+            if constexpr (V == 1) {
+              q[r][0] = __ldcs(reinterpret_cast<const unsigned short*>(src));
+            } else if constexpr (V == 2) {
+              const unsigned x = __ldcs(reinterpret_cast<const unsigned*>(src));
+              q[r][0] = x & 0xffffu; q[r][1] = x >> 16;
+            } else {
+              const uint2 x = __ldcs(reinterpret_cast<const uint2*>(src));
+              q[r][0] = x.x & 0xffffu; q[r][1] = x.x >> 16; q[r][2] = x.y & 0xffffu; q[r][3] = x.y >> 16;
+            }
+          }
+#pragma unroll
+          for (int v = 0; v < V; ++v) {
+            const unsigned w0 = q[0][v] | (q[1][v] << 16), w1 = q[2][v] | (q[3][v] << 16);
+            const unsigned p0 = ((w0 >> (5 + st[v])) & 1u) ? (unsigned)st[v] : (w0 & 31u);
+            const unsigned p1 = ((w1 >> (5 + st[v])) & 1u) ? (unsigned)st[v] : (w1 & 31u);
+            pair[v] = p0 | (p1 << 8);
+          }
+        } else {
 #pragma unroll
         for (int v = 0; v < V; ++v)
           pair[v] = __ldcs(reinterpret_cast<const unsigned short*>(arg + (((size_t)k * A + st[v]) * p.stride + v) * 2));
+        }
       }
 #pragma unroll
       for (int slot = 0; slot < 2; ++slot) {
@@ -238,12 +279,17 @@ int trex_encode_leaf_states(const float* seqs, int n_leaves, int64_t n_sites, in
   return TREX_OK;
 }
 
-int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_states,
-                           int64_t n_sites, int64_t site_stride, int batch,
-                           const uint8_t* leaf_states, const float* dp, const uint8_t* argmin,
-                           uint8_t* anc_states, unsigned long long* edge_hist, void* stream) {
+int trex_sankoff_traceback_cost(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                                int64_t n_sites, int64_t site_stride, int batch,
+                                const uint8_t* leaf_states, const float* cost, int mode, const float* dp,
+                                const uint8_t* argmin, uint8_t* anc_states, unsigned long long* edge_hist,
+                                void* stream) {
   using namespace trex;
   TREX_CHECK_ARG(plan && leaf_states && dp && argmin && anc_states, "trex_sankoff_traceback: null pointer");
+  const int want_compact = mode & TREX_MODE_COMPACT_ARG;
+  mode &= ~TREX_MODE_COMPACT_ARG;
+  TREX_CHECK_ARG(mode == TREX_MODE_AUTO || mode == TREX_MODE_GENERAL, "trex_sankoff_traceback_cost: bad mode");
+  TREX_CHECK_ARG(!want_compact || cost, "trex_sankoff_traceback_cost: TREX_MODE_COMPACT_ARG needs the cost matrix");
   TREX_CHECK_ARG(n_leaves >= 1 && n_all > n_leaves && n_states >= 1 && n_states <= 32,
                  "trex_sankoff_traceback: bad tree sizes");
   TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0,
@@ -257,24 +303,46 @@ int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_s
   }
   TraceParams p{plan, trex_sankoff_plan_words(n_all, n_leaves), n_all, n_leaves, n_states,
                 (long long)n_sites, (long long)site_stride, leaf_states, dp, argmin, anc_states, edge_hist};
+  p.phase = 0;
+  p.cost = cost;
+  p.mode = mode;
+  p.compact = want_compact && compact_arg_ok(n_states);
   constexpr int THREADS = 128;
   const size_t smem = edge_hist ? sizeof(unsigned int) * n_states * n_states : 0;
-  // One site per lane: the walk is a chain of dependent one-byte gathers, so resident warps (latency
-  // hiding) matter more than vector width; measured 1.78 -> 1.29 ms at c5 against V = 4.
-  constexpr int V = 1;
-  const unsigned gx = (unsigned)(((n_sites + V - 1) / V + THREADS - 1) / THREADS);
-  if (use_segments(n_leaves)) {
-    p.phase = 2;  // top-down: the nodes above the segments first, then the independent subtrees
-    traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
-    p.phase = 1;
-    traceback_kernel<V, THREADS><<<dim3(gx, batch, kMaxSeg), THREADS, smem, s>>>(p);
-    note_launches(2);
-  } else {
-    traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
-    note_launches(1);
-  }
+  auto run = [&](auto vc) {
+    constexpr int V = decltype(vc)::value;
+    const unsigned gx = (unsigned)(((n_sites + V - 1) / V + THREADS - 1) / THREADS);
+    if (use_segments(n_leaves)) {
+      p.phase = 2;  // top-down: the nodes above the segments first, then the independent subtrees
+      traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
+      p.phase = 1;
+      traceback_kernel<V, THREADS><<<dim3(gx, batch, kMaxSeg), THREADS, smem, s>>>(p);
+      note_launches(2);
+    } else {
+      traceback_kernel<V, THREADS><<<dim3(gx, batch), THREADS, smem, s>>>(p);
+      note_launches(1);
+    }
+  };
+  // Sites per lane.  The walk is instruction-bound (order / child look-ups and addresses per node and lane), so wide
+  // lanes win as long as enough warps remain to hide the chain of dependent reads: measured on the 1024-leaf tree
+  // (tools/probe_trace.py, pointer words, with histogram) 100k sites 0.60 / 0.45 / 0.36 ms at 1 / 2 / 4 sites per lane,
+  // 12.5k sites 0.128 / 0.102 / 0.115, 1k sites 0.066 / 0.081 / 0.098.  TREX_TRACE_V overrides (probe).
+  const long long work = (long long)n_sites * batch;
+  int v = work >= 50000 ? 4 : work >= 5000 ? 2 : 1;
+  if (const char* e = getenv("TREX_TRACE_V")) v = atoi(e);
+  if (v == 4) run(std::integral_constant<int, 4>{});
+  else if (v == 2) run(std::integral_constant<int, 2>{});
+  else run(std::integral_constant<int, 1>{});
   TREX_CHECK_LAUNCH("traceback_kernel");
   return TREX_OK;
+}
+
+int trex_sankoff_traceback(const int32_t* plan, int n_all, int n_leaves, int n_states,
+                           int64_t n_sites, int64_t site_stride, int batch,
+                           const uint8_t* leaf_states, const float* dp, const uint8_t* argmin,
+                           uint8_t* anc_states, unsigned long long* edge_hist, void* stream) {
+  return trex_sankoff_traceback_cost(plan, n_all, n_leaves, n_states, n_sites, site_stride, batch, leaf_states, nullptr,
+                                     TREX_MODE_AUTO, dp, argmin, anc_states, edge_hist, stream);
 }
 
 int trex_sankoff_export_dp(int n_all, int n_leaves, int n_states, int64_t n_sites,

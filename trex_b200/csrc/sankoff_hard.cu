@@ -372,6 +372,8 @@ extern "C" int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leave
   TREX_CHECK_ARG(n_sites >= 1 && site_stride >= n_sites && site_stride % 16 == 0 && site_stride < (1LL << 29),
                  "trex_sankoff_hard_fwd: site_stride must be a multiple of 16, >= n_sites and < 2^29");
   TREX_CHECK_ARG(batch >= 1 && batch <= 65535, "trex_sankoff_hard_fwd: batch out of range");
+  const int want_compact = mode & TREX_MODE_COMPACT_ARG;
+  mode &= ~TREX_MODE_COMPACT_ARG;
   TREX_CHECK_ARG(mode == TREX_MODE_AUTO || mode == TREX_MODE_GENERAL, "trex_sankoff_hard_fwd: bad mode");
   cudaStream_t s = (cudaStream_t)stream;
   if (total) {
@@ -381,6 +383,8 @@ extern "C" int trex_sankoff_hard_fwd(const int32_t* plan, int n_all, int n_leave
   HardFwdParams p{plan, trex_sankoff_plan_words(n_all, n_leaves), n_all, n_leaves, n_states,
                   (long long)n_sites, (long long)site_stride, leaf_states, cost, dp, argmin,
                   root_min, total, mode};
+  p.phase = 0;
+  p.compact = want_compact && argmin && compact_arg_ok(n_states);
   const int A = n_states;
   {
     // device-side dispatch on the cost matrix: the O(A) kernel returns at once unless C is uniform

@@ -99,6 +99,29 @@ __device__ __forceinline__ int pick_index_key(float d, float keyj, int j) {
   return idx;
 }
 
+// Compact back-pointers ("pointer words", TREX_MODE_COMPACT_ARG): under a uniform cost the pointer of parent state s is
+// either s itself ("stay") or the child's first minimum j, whatever s is — so one 32-bit word per (node, site, child)
+// holds all of them: bits 0-4 = j, bit 5+s = "state s stays" (n_states <= 27).  2 * n_states bytes of table per node
+// and site become 8 (rows 0-3 of the node's byte table, the other rows are not written), and the traceback reads those
+// 4 rows coalesced instead of gathering 2 bytes from one of n_states rows (32-byte sectors: 6.8x its useful bytes).  Same decisions as pick_index / pick_index_key: the bit is set exactly when they return S.
+template <int S>
+__device__ __forceinline__ void stay_bit(float d, float am, int j, unsigned& mask) {
+  asm("{\n\t.reg .pred p;\n\t"
+      "setp.le.s32 p, %3, %4;\n\t"
+      "setp.eq.and.f32 p, %1, %2, p;\n\t"
+      "setp.lt.or.f32 p, %1, %2, p;\n\t"
+      "@p or.b32 %0, %0, %5;\n\t}"
+      : "+r"(mask) : "f"(d), "f"(am), "n"(S), "r"(j), "n"(1u << (5 + S)));
+}
+template <int S>
+__device__ __forceinline__ void stay_bit_key(float d, float keyj, unsigned& mask) {
+  asm("{\n\t.reg .pred p;\n\t.reg .f32 k;\n\t"
+      "add.f32 k, %1, %2;\n\t"
+      "setp.le.f32 p, k, %3;\n\t"
+      "@p or.b32 %0, %0, %4;\n\t}"
+      : "+r"(mask) : "f"(d), "f"((float)S * 0.015625f), "f"(keyj), "n"(1u << (5 + S)));
+}
+
 // A rows of a dp node, state-major
 template <int AP, int V, bool FULL>
 __device__ __forceinline__ void load_rows(const float* __restrict__ src, int A, size_t stride, float (&d)[AP][V]) {
@@ -156,9 +179,10 @@ __device__ __forceinline__ void leaf_first_min(const int (&o)[V], int A, float a
 
 }  // namespace
 
-// FULL: n_states == AP (no padded state rows); WANT_ARG: the traceback tables are written.
-template <int AP, int V, int THREADS, bool FULL, bool WANT_ARG>
+// FULL: n_states == AP (no padded state rows); WANT_ARG: the traceback tables are written; COMPACT: as pointer words.
+template <int AP, int V, int THREADS, bool FULL, bool WANT_ARG, bool COMPACT = false>
 __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwdParams p) {
+  static_assert(!COMPACT || (WANT_ARG && AP <= 27), "pointer words: 5 + n_states bits");
   float a;
   if (p.phase == 1 && (int)blockIdx.z >= (p.plan + (size_t)blockIdx.y * p.plan_words)[2]) return;  // empty segment slice (CTA-uniform): before any other work
   if (!hard_uniform_applies(p, a)) return;
@@ -247,6 +271,9 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
         kjy[v] = fmaf((float)jy[v], 0.015625f, amy[v]);
       }
       small = WANT_ARG && __all_sync(walkers, small);
+      unsigned mx[V], my[V];  // COMPACT: the "stays" bits of the two children
+#pragma unroll
+      for (int v = 0; v < V; ++v) mx[v] = my[v] = 0u;
       auto state_rows = [&](auto keyed) {
       static_for<AP>([&](auto sc) {
         constexpr int s = decltype(sc)::value;
@@ -254,7 +281,15 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
           int ix[V], iy[V];
 #pragma unroll
           for (int v = 0; v < V; ++v) {
-            if (WANT_ARG) {
+            if constexpr (COMPACT) {
+              if constexpr (decltype(keyed)::value) {
+                stay_bit_key<s>(dx[s][v], kjx[v], mx[v]);
+                stay_bit_key<s>(dy[s][v], kjy[v], my[v]);
+              } else {
+                stay_bit<s>(dx[s][v], amx[v], jx[v], mx[v]);
+                stay_bit<s>(dy[s][v], amy[v], jy[v], my[v]);
+              }
+            } else if (WANT_ARG) {
               if constexpr (decltype(keyed)::value) {
                 ix[v] = pick_index_key<s>(dx[s][v], kjx[v], jx[v]);
                 iy[v] = pick_index_key<s>(dy[s][v], kjy[v], jy[v]);
@@ -267,13 +302,39 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
             dx[s][v] = fminf(dx[s][v], amx[v]) + fminf(dy[s][v], amy[v]);
           }
           st_f<V>(out + (size_t)s * stride, dx[s]);
-          if (WANT_ARG) st_arg_pair<V>(aout + (size_t)s * 2 * stride, ix, iy, x_first);
+          if (WANT_ARG && !COMPACT) st_arg_pair<V>(aout + (size_t)s * 2 * stride, ix, iy, x_first);
           if (reload) ld_f<V>(nsrc + (size_t)s * stride, dy[s]);
         }
       });
       };
       if (small) state_rows(std::true_type{});
       else state_rows(std::false_type{});
+      if constexpr (COMPACT) {
+        // rows 0-3 of this node's byte table take the four 16-bit quarters of (word of slot 0, word of slot 1): any
+        // pointer arithmetic that is right for the byte table (tree batches, site blocks) is right for the words.
+        // slot 0 = first child (sankoff.py:80-83); jx / jy are this node's (decode(i + 1) does not touch them)
+        unsigned w0[V], w1[V];
+#pragma unroll
+        for (int v = 0; v < V; ++v) {
+          const unsigned wx = mx[v] | (unsigned)jx[v], wy = my[v] | (unsigned)jy[v];
+          w0[v] = x_first ? wx : wy;
+          w1[v] = x_first ? wy : wx;
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          uint8_t* dst = aout + (size_t)r * 2 * stride;
+          const unsigned sel = (r & 1) ? 0x7632u : 0x5410u;  // high / low halves of two words
+          if constexpr (V == 1) {
+            __stcs(reinterpret_cast<unsigned short*>(dst), (unsigned short)(((r < 2 ? w0[0] : w1[0]) >> (16 * (r & 1))) & 0xffffu));
+          } else if constexpr (V == 2) {
+            __stcs(reinterpret_cast<unsigned*>(dst), r < 2 ? __byte_perm(w0[0], w0[1], sel) : __byte_perm(w1[0], w1[1], sel));
+          } else {
+            __stcs(reinterpret_cast<uint2*>(dst),
+                   r < 2 ? make_uint2(__byte_perm(w0[0], w0[1], sel), __byte_perm(w0[2], w0[3], sel))
+                         : make_uint2(__byte_perm(w1[0], w1[1], sel), __byte_perm(w1[2], w1[3], sel)));
+          }
+        }
+      }
     }
     // per-site root minimum (sankoff.py:187): the root's row is still in dx unless nodes the root does
     // not reach followed it in the walk
@@ -510,7 +571,12 @@ void launch_hard_uniform(const HardFwdParams& p0, int batch, cudaStream_t s) {
   const unsigned gx = (unsigned)((p0.n_sites + (long long)T * V - 1) / ((long long)T * V));
   const bool full = p0.n_states == AP;
   auto run = [&](const HardFwdParams& p, dim3 grid) {
-    if (p.arg) {
+    if (p.arg && p.compact) {
+      if constexpr (AP <= 27) {
+        if (full) { hard_fwd_uniform_kernel<AP, V, T, true, true, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+        else { hard_fwd_uniform_kernel<AP, V, T, false, true, true><<<grid, T, 0, s>>>(p); note_launches(1); }
+      }
+    } else if (p.arg) {
       if (full) { hard_fwd_uniform_kernel<AP, V, T, true, true><<<grid, T, 0, s>>>(p); note_launches(1); }
       else { hard_fwd_uniform_kernel<AP, V, T, false, true><<<grid, T, 0, s>>>(p); note_launches(1); }
     } else {

@@ -171,8 +171,14 @@ class SankoffEngine:
     return self
 
   # -- kernels ------------------------------------------------------------------------------
-  def hard_forward(self, cost, want_argmin=True, mode=_lib.MODE_AUTO):
+  def hard_forward(self, cost, want_argmin=True, mode=_lib.MODE_AUTO, compact_arg=True):
+    """``compact_arg``: let the library write the back-pointers as pointer words when the cost matrix is uniform
+    (``TREX_MODE_COMPACT_ARG``, include/trex_b200.h: 8 instead of 2A bytes per node and site); ``traceback`` reads
+    either form, ``export_bt`` needs ``compact_arg=False``."""
     cost = cost.to(device=self.device, dtype=torch.float32).contiguous()
+    if want_argmin:
+      mode = mode | (_lib.MODE_COMPACT_ARG if compact_arg else 0)
+      self._arg_cost, self._arg_mode = cost, mode  # the traceback repeats the forward's decision on the same matrix
     call("trex_sankoff_hard_fwd", ptr(self.plan), self.n_all, self.n_leaves, self.A, self.L,
          self.stride, self.batch, ptr(self.leaf), ptr(cost), ptr(self.dp),
          ptr(self.argmin) if want_argmin else None, ptr(self.root_min), ptr(self.total), mode,
@@ -180,8 +186,9 @@ class SankoffEngine:
     return self.total
 
   def traceback(self, want_hist=False):
-    call("trex_sankoff_traceback", ptr(self.plan), self.n_all, self.n_leaves, self.A, self.L,
-         self.stride, self.batch, ptr(self.leaf), ptr(self.dp), ptr(self.argmin), ptr(self.anc),
+    cost, mode = getattr(self, "_arg_cost", None), getattr(self, "_arg_mode", _lib.MODE_AUTO)
+    call("trex_sankoff_traceback_cost", ptr(self.plan), self.n_all, self.n_leaves, self.A, self.L,
+         self.stride, self.batch, ptr(self.leaf), ptr(cost), mode, ptr(self.dp), ptr(self.argmin), ptr(self.anc),
          ptr(self.edge_hist) if want_hist else None, stream_ptr())
     return self.anc
 
@@ -228,10 +235,35 @@ class SankoffEngine:
          ptr(self.leaf), ptr(self.anc[tree]) if with_path else None, ptr(out), stream_ptr())
     return out
 
+  def wrote_pointer_words(self) -> bool:
+    """Whether the last ``hard_forward(want_argmin=True)`` left pointer words in ``argmin`` — the device-side test
+    of include/trex_b200.h (TREX_MODE_COMPACT_ARG) repeated on the host; copies the cost matrix back (a sync): for
+    exports and tests, not for the hot path."""
+    mode = getattr(self, "_arg_mode", 0)
+    if not (mode & _lib.MODE_COMPACT_ARG) or (mode & 0xff) != _lib.MODE_AUTO or not 4 <= self.A <= 20:
+      return False
+    c = self._arg_cost.cpu()
+    a = float(c[0, 1])
+    want = a * (1.0 - torch.eye(self.A))
+    return bool(torch.equal(c, want)) and 0.0 <= a < 65536.0 and a == int(a) and a * self.n_all < 262000.0
+
+  def argmin_table(self):
+    """The back-pointers as the byte table u8 [batch][n_int][A][stride][2], whichever form ``hard_forward`` wrote
+    (pointer words are decoded with torch ops into a new tensor)."""
+    if not self.wrote_pointer_words():
+      return self.argmin
+    q = self.argmin[:, :, :4].to(torch.int64)                       # rows 0-3: [B][n_int][4][stride][2] bytes
+    q16 = q[..., 0] | (q[..., 1] << 8)                              # [B][n_int][4][stride]
+    words = torch.stack([q16[:, :, 0] | (q16[:, :, 1] << 16), q16[:, :, 2] | (q16[:, :, 3] << 16)], dim=-1)
+    words = words[:, :, None]                                       # [B][n_int][1][stride][2]
+    s = torch.arange(self.A, device=self.device).view(1, 1, self.A, 1, 1)
+    return torch.where(((words >> (5 + s)) & 1).bool(), s, words & 31).to(torch.uint8)
+
   def export_bt(self, tree=0):
     out = torch.empty((self.L, self.n_all, self.A, 4), dtype=torch.float32, device=self.device)
+    table = self.argmin_table()[tree].contiguous()
     call("trex_sankoff_export_bt", ptr(self.plan[tree]), self.n_all, self.n_leaves, self.A,
-         self.L, self.stride, ptr(self.argmin[tree]), ptr(out), stream_ptr())
+         self.L, self.stride, ptr(table), ptr(out), stream_ptr())
     return out
 
   def plan_status(self, tree=0):
@@ -276,7 +308,7 @@ def vectorized_dp(adjacency_matrix, dynamic_programming_table, backtracking_tabl
   eng = SankoffEngine(n_all, n_leaves, A, L)
   eng.set_adjacency(torch.as_tensor(adjacency_matrix), zero_root_selfloop=False)
   eng.set_sequences_f32(torch.as_tensor(sequences))
-  eng.hard_forward(torch.as_tensor(cost_matrix), want_argmin=True)
+  eng.hard_forward(torch.as_tensor(cost_matrix), want_argmin=True, compact_arg=False)
   return eng.export_dp(), eng.export_bt()
 
 
