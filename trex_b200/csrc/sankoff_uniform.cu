@@ -274,6 +274,36 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
       unsigned mx[V], my[V];  // COMPACT: the "stays" bits of the two children
 #pragma unroll
       for (int v = 0; v < V; ++v) mx[v] = my[v] = 0u;
+      if constexpr (COMPACT) {
+        // Before the state loop (which overwrites dx and reloads dy).  A leaf child needs no compares: its row is 0 at
+        // the observed state o and 1e5 elsewhere, so for a > 0 only state o stays (0 < a; 1e5 > a + 0), and a
+        // stateless leaf (all 1e5 < a + 1e5) makes every state stay.  Half of a binary tree's children are leaves.
+        auto masks = [&](const float (&d)[AP][V], const float (&am)[V], const float (&kj)[V], const int (&j)[V],
+                         bool leaf, unsigned (&m)[V]) {
+          if (leaf && a > 0.f) {
+#pragma unroll
+            for (int v = 0; v < V; ++v) m[v] = am[v] >= kSentinel ? (((1u << A) - 1u) << 5) : (1u << (5 + j[v]));
+          } else if (small) {
+            static_for<AP>([&](auto sc) {
+              constexpr int s = decltype(sc)::value;
+              if (FULL || s < A) {
+#pragma unroll
+                for (int v = 0; v < V; ++v) stay_bit_key<s>(d[s][v], kj[v], m[v]);
+              }
+            });
+          } else {
+            static_for<AP>([&](auto sc) {
+              constexpr int s = decltype(sc)::value;
+              if (FULL || s < A) {
+#pragma unroll
+                for (int v = 0; v < V; ++v) stay_bit<s>(d[s][v], am[v], j[v], m[v]);
+              }
+            });
+          }
+        };
+        masks(dx, amx, kjx, jx, x_leaf, mx);
+        masks(dy, amy, kjy, jy, y_leaf, my);
+      }
       auto state_rows = [&](auto keyed) {
       static_for<AP>([&](auto sc) {
         constexpr int s = decltype(sc)::value;
@@ -282,13 +312,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
 #pragma unroll
           for (int v = 0; v < V; ++v) {
             if constexpr (COMPACT) {
-              if constexpr (decltype(keyed)::value) {
-                stay_bit_key<s>(dx[s][v], kjx[v], mx[v]);
-                stay_bit_key<s>(dy[s][v], kjy[v], my[v]);
-              } else {
-                stay_bit<s>(dx[s][v], amx[v], jx[v], mx[v]);
-                stay_bit<s>(dy[s][v], amy[v], jy[v], my[v]);
-              }
+              // the words were taken before this loop
             } else if (WANT_ARG) {
               if constexpr (decltype(keyed)::value) {
                 ix[v] = pick_index_key<s>(dx[s][v], kjx[v], jx[v]);
@@ -307,7 +331,7 @@ __global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwd
         }
       });
       };
-      if (small) state_rows(std::true_type{});
+      if (small && !COMPACT) state_rows(std::true_type{});
       else state_rows(std::false_type{});
       if constexpr (COMPACT) {
         // rows 0-3 of this node's byte table take the four 16-bit quarters of (word of slot 0, word of slot 1): any
