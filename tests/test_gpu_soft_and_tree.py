@@ -337,3 +337,51 @@ def test_reverse_pass_poisons_dcost_when_the_adjacency_is_not_a_tree(ck, A, T, k
   assert abs(float(eng.soft_total[0]) - tot64) <= RTOL * abs(tot64)
   eng.soft_backward(torch.from_numpy(cost), T, want_dleaf="compact")
   assert bool(torch.isnan(eng.dcost[0]).all())
+
+
+@pytest.mark.parametrize("N,L,Q", [(127, 1000, 4), (5, 7, 4), (128, 40, 20), (64, 500, 4), (100, 3000, 4)])
+def test_tree_cost_one_kernel_mode_vs_three_kernel_chain_and_oracle(N, L, Q, monkeypatch):
+  """One-kernel mode of the tcgen05 path (tree_cost_tc.cu: tagged flags, per-slice slots, launch counter kept on the
+  device) against the three-kernel chain and float64 (tree.py:163-266): one workspace reused over many calls with
+  changing inputs, value-only calls in between, and a CUDA-graph replay (same kernel arguments every replay)."""
+  import torch
+  from trex_b200._lib import load
+  from trex_b200.tree import tree_cost_value_and_grad
+
+  lib = load()
+  ws = torch.empty(lib.trex_tree_cost_workspace_bytes(N, L * Q, Q), dtype=torch.uint8, device="cuda")
+  ws.random_(0, 256)                                             # a fresh workspace holds anything
+  launches = {}
+  for rep in range(4):
+    S, adj, _ = _tree_inputs(N, L, Q, seed=7 * N + L + Q + rep, adj_kind="bernoulli")
+    want, dS64, dA64, _ = to.soft_cost_value_and_grad(S, adj, None)
+    _, (t1, t2, t3) = to.compute_soft_cost(S, adj, None, dtype=np.float64)
+    bound = RTOL * abs(want) + 4 * np.finfo(np.float32).eps * (abs(t1) + abs(t2) + abs(t3))
+    St, At = torch.from_numpy(S).cuda(), torch.from_numpy(adj).cuda()
+    for one in ("1", "0"):
+      monkeypatch.setenv("TREX_TREE_COST_ONE", one)
+      before = lib.trex_kernel_launches()
+      cost, dS, dA, _ = tree_cost_value_and_grad(St, At, None, workspace=ws)
+      launches[one] = lib.trex_kernel_launches() - before
+      torch.cuda.synchronize()
+      assert abs(float(cost) - want) <= bound, (rep, one)
+      assert _relerr(dS.cpu().numpy(), dS64) <= RTOL, (rep, one)
+      assert _relerr(dA.cpu().numpy(), dA64) <= RTOL, (rep, one)
+      c2, _, _, _ = tree_cost_value_and_grad(St, At, None, want_dseq=False, want_dadj=False, workspace=ws)
+      assert abs(float(c2) - want) <= bound, (rep, one)
+  assert launches["1"] == 1 and launches["0"] >= 2
+  # graph replay: the launch counter advances on the device, so identical launches stay correct
+  monkeypatch.setenv("TREX_TREE_COST_ONE", "1")
+  out = {"cost": torch.empty((), device="cuda"), "dS": torch.empty_like(St), "dA": torch.empty_like(At)}
+  stream = torch.cuda.Stream()
+  with torch.cuda.stream(stream):
+    tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=stream):
+      tree_cost_value_and_grad(St, At, None, workspace=ws, out=out)
+    for _ in range(5):
+      out["cost"].zero_(); out["dS"].zero_(); out["dA"].zero_()
+      g.replay()
+  torch.cuda.synchronize()
+  assert abs(float(out["cost"]) - want) <= bound
+  assert _relerr(out["dS"].cpu().numpy(), dS64) <= RTOL and _relerr(out["dA"].cpu().numpy(), dA64) <= RTOL

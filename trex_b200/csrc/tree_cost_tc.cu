@@ -155,6 +155,35 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n, bool a_mn_m
 
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
+// ---- one-kernel mode: tagged flags instead of kernel boundaries ---------------------------------
+// A flag holds (magic << 32 | launch number); the launch number lives in device memory and is advanced by the
+// kernel itself, so nothing has to be zeroed between launches and a replayed CUDA graph works.  The magic makes a
+// stale match in a fresh (uninitialised) workspace a 2^-64 event.
+constexpr unsigned long long kTagMagic = 0x7452655800000000ull;
+__device__ __forceinline__ void flag_publish(unsigned long long* f, unsigned long long tag) {
+  __threadfence();
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(f), "l"(tag) : "memory");
+}
+__device__ __forceinline__ unsigned long long flag_peek(const unsigned long long* f) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+  return v;
+}
+// Thread `t` of `nthreads` watches flags t, t + nthreads, ...; returns false (and raises *err) when a flag does not
+// arrive within ~1 s — only possible if the grid is not co-resident, which the launcher rules out.
+__device__ __forceinline__ bool flags_watch(const unsigned long long* f, int n, unsigned long long tag, int t, int nthreads,
+                                            unsigned* err) {
+  bool ok = true;
+  for (int i = t; i < n && ok; i += nthreads) {
+    unsigned spins = 0;
+    while (flag_peek(f + i) != tag) {
+      if (++spins > (1u << 21)) { ok = false; atomicExch(err, 1u); break; }
+    }
+  }
+  __threadfence();  // acquire: what the publishers wrote before their flags is visible from here on
+  return ok;
+}
+
 // ---------------------------------------------------------------------------------------------
 // prep kernel: row i of Msym = M + M^T (tf32 head / remainder), d_i, zero G.  grid = Npad, block = 256
 // ---------------------------------------------------------------------------------------------
@@ -233,6 +262,9 @@ struct GemmParams {
   unsigned* ticket;     // zeroed by the prep kernel
   float* out_cost;
   float* d_adj;
+  // one-kernel mode
+  int one;
+  TcBuffers w;
 };
 
 template <int NPAD>
@@ -271,6 +303,35 @@ __global__ void __launch_bounds__(256, 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   pdl_launch_dependents();
+  const unsigned long long tag = p.one ? (kTagMagic | (unsigned long long)(*(volatile unsigned*)p.w.epoch + 1u)) : 0ull;
+  if (p.one && !is_gram) {
+    // ===== one-kernel mode, dS units: the rows of Msym = M + M^T (what prep_kernel does), a warp per row =====
+    const int N = p.n_nodes;
+    for (int r = unit + warp * p.n_ds; r < NPAD; r += p.n_ds * (Cfg::THREADS / 32)) {
+      float a[4], at[4];  // adj[r][j], adj[j][r] for j = lane + 32 q: read once, all eight loads in flight
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int j = lane + 32 * q;
+        const bool on = r < N && j < N;
+        a[q] = on ? __ldg(p.adj + (size_t)r * N + j) : 0.f;
+        at[q] = on ? __ldg(p.adj + (size_t)j * N + r) : 0.f;
+      }
+      float acc = (a[0] + at[0]) + (a[1] + at[1]) + (a[2] + at[2]) + (a[3] + at[3]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      const float dr = 0.5f * acc;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int j = lane + 32 * q;
+        const float m = (r < N && j < N) ? (r == j ? 2.f * dr : 0.f) - a[q] - at[q] : 0.f;
+        const float hi = tf32_hi(m);
+        p.w.m_hi[(size_t)r * NPAD + j] = hi;
+        p.w.m_lo[(size_t)r * NPAD + j] = m - hi;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) flag_publish(p.w.flags + unit, tag);
+  }
   // What the prep kernel produces is needed late: Msym by the dS producer's B loads, the zeroed G and the
   // ticket by the gram epilogue.  S itself is the caller's tensor, so the main loop of the gram units and
   // the A loads of the dS units overlap the prep kernel (pdl_wait() at the points of use).
@@ -284,24 +345,38 @@ __global__ void __launch_bounds__(256, 1)
     it1 = NPAD / Cfg::BK;
   }
 
-  if (warp == 0 && lane == 0) {
-    // ===== TMA producer =====
+  if (warp == 0 && (lane == 0 || (p.one && !is_gram))) {
+    // ===== TMA producer (lane 0; in one-kernel mode the other lanes of the warp help to watch the flags) =====
     int stage = 0;
     uint32_t phase = 0;
     for (int it = it0; it < it1; ++it) {
-      mbar_wait(empty_bar + stage, phase ^ 1);
       uint8_t* st = tiles + stage * Cfg::STAGE_BYTES;
-      if (is_gram) {
-        mbar_expect_tx(full_bar + stage, Cfg::B_BYTES);
-        tma_load_2d(st + 2 * Cfg::A_BYTES, &map_s_gram, full_bar + stage, it * Cfg::BK, 0);
-      } else {
-        mbar_expect_tx(full_bar + stage, Cfg::A_BYTES + 2 * Cfg::B_BYTES);
+      if (lane == 0) {
+        mbar_wait(empty_bar + stage, phase ^ 1);
+        if (is_gram) {
+          mbar_expect_tx(full_bar + stage, Cfg::B_BYTES);
+          tma_load_2d(st + 2 * Cfg::A_BYTES, &map_s_gram, full_bar + stage, it * Cfg::BK, 0);
+        } else {
+          mbar_expect_tx(full_bar + stage, Cfg::A_BYTES + 2 * Cfg::B_BYTES);
 #pragma unroll
-        for (int c = 0; c < 4; ++c)  // [32 node rows][32 columns] boxes: chunk c of the 128 columns
-          tma_load_2d(st + c * 4096, &map_s_ds, full_bar + stage, unit * 128 + c * 32, it * Cfg::BK);
-        if (it == it0) pdl_wait();  // Msym tiles come from the prep kernel
-        tma_load_2d(st + 2 * Cfg::A_BYTES, &map_m_hi, full_bar + stage, it * Cfg::BK, 0);
-        tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &map_m_lo, full_bar + stage, it * Cfg::BK, 0);
+          for (int c = 0; c < 4; ++c)  // [32 node rows][32 columns] boxes: chunk c of the 128 columns
+            tma_load_2d(st + c * 4096, &map_s_ds, full_bar + stage, unit * 128 + c * 32, it * Cfg::BK);
+        }
+      }
+      if (!is_gram) {
+        if (it == it0) {
+          if (p.one) {  // Msym rows come from the dS units of this grid: all of them must have published
+            flags_watch(p.w.flags, p.n_ds, tag, lane, 32, p.w.err);
+            __syncwarp();
+            asm volatile("fence.proxy.async;" ::: "memory");  // generic-proxy writes (other CTAs) before this CTA's TMA reads
+          } else if (lane == 0) {
+            pdl_wait();  // Msym tiles come from the prep kernel
+          }
+        }
+        if (lane == 0) {
+          tma_load_2d(st + 2 * Cfg::A_BYTES, &map_m_hi, full_bar + stage, it * Cfg::BK, 0);
+          tma_load_2d(st + 2 * Cfg::A_BYTES + Cfg::B_BYTES, &map_m_lo, full_bar + stage, it * Cfg::BK, 0);
+        }
       }
       if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
     }
@@ -372,7 +447,36 @@ __global__ void __launch_bounds__(256, 1)
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-    if (is_gram) {
+    if (is_gram && p.one) {
+      // one-kernel mode: the partial G of this split-K slice goes to the slice's own slot (no atomics, nothing to zero).
+      // A TMEM lane is a row, so a lane holds 32 columns of ONE row; the warp transposes 32 x 32 blocks through the
+      // (now idle) stage memory so that a store instruction writes four full 128-byte row segments.
+      constexpr int PITCH = 36;  // floats: 16-byte aligned rows, conflict-free 128-bit accesses per quarter-warp
+      float* tr = reinterpret_cast<float*>(tiles) + warp * 32 * PITCH;
+      float* slot = p.w.slots + ((size_t)unit * 128 + warp * 32) * 128;
+#pragma unroll 1
+      for (int c0 = 0; c0 < 128; c0 += 32) {
+        float v[32];
+        tmem_ld32(tmem_base + lane_base + c0, v);
+        if (c0 == warp * 32) {  // the diagonal element of row r = 32 * warp + lane sits at column c0 + lane
+          float dg = 0.f;
+#pragma unroll
+          for (int q = 0; q < 32; ++q) dg = q == lane ? v[q] : dg;
+          p.w.diag_part[unit * 128 + warp * 32 + lane] = dg;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 32; q += 4)
+          *reinterpret_cast<float4*>(tr + lane * PITCH + q) = make_float4(v[q], v[q + 1], v[q + 2], v[q + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int ps = 0; ps < 8; ++ps) {
+          const int rr = ps * 4 + (lane >> 3), cq = (lane & 7) * 4;
+          const float4 x = *reinterpret_cast<const float4*>(tr + rr * PITCH + cq);
+          *reinterpret_cast<float4*>(slot + (size_t)rr * 128 + c0 + cq) = x;
+        }
+      }
+    } else if (is_gram) {
       // partial G of this split-K slice -> G with 128-bit fire-and-forget reductions
       pdl_wait();  // G was zeroed (and the ticket reset) by the prep kernel
       float* row = p.g + (size_t)(mblk * 128 + warp * 32 + lane) * NPAD;
@@ -403,6 +507,88 @@ __global__ void __launch_bounds__(256, 1)
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+
+  // ===== one-kernel mode: the gram units finish the call themselves =====
+  // G = sum of the slots; cost = <M, G>; dAdj_ij = (G_ii + G_jj)/2 - G_ij.  Rows are dealt round-robin to the gram
+  // units, two rows per pass (one per half of the CTA); partial costs meet in unit 0, summed in a fixed order.
+  if constexpr (NPAD == 128) {
+  if (p.one && is_gram) {
+    __shared__ float s_diag1[128];
+    __shared__ double s_part[Cfg::THREADS / 32];
+    const int N = p.n_nodes, G = p.n_gram;
+    if (threadIdx.x == 0) flag_publish(p.w.flags + kOneMaxCtas + unit, tag);  // after the __syncthreads above: slot complete
+    flags_watch(p.w.flags + kOneMaxCtas, G, tag, threadIdx.x, Cfg::THREADS, p.w.err);
+    __syncthreads();
+    // A warp per row, a lane per 4 columns.  All loads of a pass — the slices' diagonals and the slot rows — are issued
+    // before anything is used: the pass costs one L2 round trip (it is bound by latency, not by bytes).
+    float dgx[kOneMaxGram];
+#pragma unroll
+    for (int g = 0; g < kOneMaxGram; ++g)
+      dgx[g] = (g < G && threadIdx.x < 128) ? __ldcg(p.w.diag_part + g * 128 + threadIdx.x) : 0.f;
+    double part = 0.0;
+    bool first = true;
+    for (int i = unit + warp * G; i < N || first; i += G * (Cfg::THREADS / 32)) {
+      const int j0 = 4 * lane;
+      const bool row_on = i < N;
+      float4 x[kOneMaxGram];
+      const float4* src = reinterpret_cast<const float4*>(p.w.slots + (size_t)(row_on ? i : 0) * 128 + j0);
+#pragma unroll
+      for (int g = 0; g < kOneMaxGram; ++g)
+        x[g] = (g < G && row_on) ? __ldcg(src + (size_t)g * (128 * 128 / 4)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float aij[4], aji[4], gij[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const bool on = row_on && j0 + c < N;
+        aij[c] = on ? __ldg(p.adj + (size_t)i * N + j0 + c) : 0.f;
+        aji[c] = on ? __ldg(p.adj + (size_t)(j0 + c) * N + i) : 0.f;
+      }
+      if (first) {  // CTA-uniform: every warp runs the first pass, with or without a row
+        float dsum = 0.f;
+#pragma unroll
+        for (int g = 0; g < kOneMaxGram; ++g) dsum += dgx[g];
+        if (threadIdx.x < 128) s_diag1[threadIdx.x] = dsum;
+        __syncthreads();
+        first = false;
+      }
+      if (!row_on) continue;
+#pragma unroll
+      for (int g = 0; g < kOneMaxGram; ++g) { gij[0] += x[g].x; gij[1] += x[g].y; gij[2] += x[g].z; gij[3] += x[g].w; }
+      float rs = (aij[0] + aji[0]) + (aij[1] + aji[1]) + (aij[2] + aji[2]) + (aij[3] + aji[3]);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+      const float di = 0.5f * rs;  // (row sum + column sum) / 2
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int j = j0 + c;
+        if (j < N) {
+          part += ((i == j ? (double)di : 0.0) - (double)aij[c]) * (double)gij[c];
+          if (p.d_adj) p.d_adj[(size_t)i * N + j] = 0.5f * (s_diag1[i] + s_diag1[j]) - gij[c];
+        }
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (lane == 0) s_part[warp] = part;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int q = 0; q < Cfg::THREADS / 32; ++q) t += s_part[q];
+      p.w.cost_part[unit] = t;
+      flag_publish(p.w.flags + 2 * kOneMaxCtas + unit, tag);
+    }
+    if (unit == 0) {
+      flags_watch(p.w.flags + 2 * kOneMaxCtas, G, tag, threadIdx.x, Cfg::THREADS, p.w.err);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int g = 0; g < G; ++g) t += __ldcg(p.w.cost_part + g);
+        *p.out_cost = (float)t;
+        *(volatile unsigned*)p.w.epoch = (unsigned)(tag & 0xffffffffull);  // the next launch's flags differ from every one of this launch
+      }
+    }
+    return;
+  }
+  }
 
   // ===== fused finalisation: cost = <M, G>, dAdj_ij = (G_ii + G_jj)/2 - G_ij =====
   // Every gram CTA takes a ticket after its reductions into G; the last one sees the complete G
@@ -517,6 +703,12 @@ static TcBuffers carve(void* ws, int n_nodes) {
   w.m_hi = (float*)take(nn);
   w.m_lo = (float*)take(nn);
   w.g = (float*)take(nn);
+  w.epoch = (unsigned*)take(4);
+  w.err = (unsigned*)take(4);
+  w.flags = (unsigned long long*)take(sizeof(unsigned long long) * 3 * kOneMaxCtas);
+  w.cost_part = (double*)take(sizeof(double) * kOneMaxCtas);
+  w.diag_part = (float*)take(sizeof(float) * kOneMaxGram * 128);
+  w.slots = (float*)take(sizeof(float) * (size_t)kOneMaxGram * 128 * 128);
   return w;
 }
 
@@ -524,7 +716,9 @@ size_t workspace_bytes(int n_nodes, long long k) {
   if (n_nodes < 1 || n_nodes > kMaxNodes || k < 1) return 0;
   const int npad = pad_nodes(n_nodes);
   const size_t nn = align256(sizeof(float) * (size_t)npad * npad);
-  return 256 * 2 + align256(sizeof(float) * kMaxNodes) + 3 * nn + 256;
+  const size_t one = 256 * 2 + align256(sizeof(unsigned long long) * 3 * kOneMaxCtas) + align256(sizeof(double) * kOneMaxCtas) +
+                     align256(sizeof(float) * kOneMaxGram * 128) + align256(sizeof(float) * (size_t)kOneMaxGram * 128 * 128);
+  return 256 * 2 + align256(sizeof(float) * kMaxNodes) + 3 * nn + one + 256;
 }
 
 bool supported(const float* seqs, int n_nodes, long long k, int cost_kind) {
@@ -592,7 +786,7 @@ static cudaLaunchConfig_t pdl_config(dim3 grid, dim3 block, size_t smem, cudaStr
 }
 
 template <int NPAD>
-static int launch_gemm(const float* seqs, const TcBuffers& w, const GemmParams& gp, cudaStream_t stream) {
+static int launch_gemm(const float* seqs, const TcBuffers& w, const GemmParams& gp, cudaStream_t stream, bool pdl = true) {
   CUtensorMap ms_gram, ms_ds, mm_hi, mm_lo;
   int rc;
   if ((rc = make_map(&ms_gram, seqs, gp.n_nodes, gp.k, gp.k, NPAD))) return rc;  // [Npad rows][32 cols]
@@ -605,14 +799,54 @@ static int launch_gemm(const float* seqs, const TcBuffers& w, const GemmParams& 
   if (rc) return rc;
   cudaLaunchConfig_t cfg = pdl_config(dim3(gp.n_gram * GemmCfg<NPAD>::MBLK + gp.n_ds), dim3(GemmCfg<NPAD>::THREADS),
                                       GemmCfg<NPAD>::SMEM_BYTES, stream);
+  if (!pdl) cfg.numAttrs = 0;  // a stand-alone kernel has no griddepcontrol.wait: it must not start before its predecessors end
   rc = check_cuda(cudaLaunchKernelEx(&cfg, kern, ms_gram, ms_ds, mm_hi, mm_lo, gp), "tc_gemm_kernel");
   note_launches(1);
   return rc;
 }
 
+// One-kernel mode (the c2 shape 127 x 1000 x 4): small calls are bound by launches and by the split-K
+// atomics, not by the tensor pipe.  When the whole grid fits the SMs at once (1 CTA per SM), the dS units build Msym
+// themselves, every gram unit stores its partial tile to a slot of its own, and the gram units finish <M, G> and dAdj
+// behind tagged flags — no prep / final launches, no red.global.add, no zeroing.  TREX_TREE_COST_ONE=0 keeps the
+// three-kernel chain (tests compare the two).
+static bool one_kernel_plan(int n_nodes, long long k, bool want_ds, GemmParams& gp) {
+  const char* e = getenv("TREX_TREE_COST_ONE");
+  if (e && e[0] == '0') return false;
+  if (pad_nodes(n_nodes) != 128) return false;
+  const int n_kb = (int)((k + 31) / 32);
+  int kb_per = (n_kb + kOneMaxGram - 1) / kOneMaxGram;
+  if (kb_per < 2) kb_per = 2;
+  const int n_gram = (n_kb + kb_per - 1) / kb_per;
+  const int n_ds = want_ds ? (int)((k + 127) / 128) : 0;
+  if (n_gram + n_ds > sm_count() || n_gram + n_ds > kOneMaxCtas) return false;
+  gp.n_kb = n_kb;
+  gp.kb_per_gram = kb_per;
+  gp.n_gram = n_gram;
+  gp.n_ds = n_ds;
+  return true;
+}
+
 int run(const float* seqs, const float* adj, int n_nodes, long long k, float* out_cost, float* d_seqs, float* d_adj,
         void* workspace, cudaStream_t stream) {
   TcBuffers w = carve(workspace, n_nodes);
+  {
+    GemmParams gp{};
+    if (one_kernel_plan(n_nodes, k, d_seqs != nullptr, gp)) {
+      gp.n_nodes = n_nodes;
+      gp.k = k;
+      gp.g = w.g;
+      gp.d_seqs = d_seqs;
+      gp.adj = adj;
+      gp.d = w.d;
+      gp.ticket = w.ticket;
+      gp.out_cost = out_cost;
+      gp.d_adj = d_adj;
+      gp.one = 1;
+      gp.w = w;
+      return launch_gemm<128>(seqs, w, gp, stream, /*pdl=*/false);
+    }
+  }
   prep_kernel<<<w.npad, 256, 0, stream>>>(adj, n_nodes, w);
   note_launches(1);
   TREX_CHECK_LAUNCH("tc::prep_kernel");
