@@ -181,7 +181,7 @@ __device__ __forceinline__ void leaf_first_min(const int (&o)[V], int A, float a
 
 // FULL: n_states == AP (no padded state rows); WANT_ARG: the traceback tables are written; COMPACT: as pointer words.
 template <int AP, int V, int THREADS, bool FULL, bool WANT_ARG, bool COMPACT = false>
-__global__ void __launch_bounds__(THREADS) hard_fwd_uniform_kernel(const HardFwdParams p) {
+__global__ void __launch_bounds__(THREADS, 4) hard_fwd_uniform_kernel(const HardFwdParams p) {
   static_assert(!COMPACT || (WANT_ARG && AP <= 27), "pointer words: 5 + n_states bits");
   float a;
   if (p.phase == 1 && (int)blockIdx.z >= (p.plan + (size_t)blockIdx.y * p.plan_words)[2]) return;  // empty segment slice (CTA-uniform): before any other work
@@ -432,7 +432,7 @@ __device__ __forceinline__ void leaf_exp_domain(const int (&o)[V], int A, float 
 }  // namespace
 
 template <int AP, int V, int THREADS, bool FULL>
-__global__ void __launch_bounds__(THREADS) soft_fwd_uniform_kernel(const SoftFwdParams p) {
+__global__ void __launch_bounds__(THREADS, 4) soft_fwd_uniform_kernel(const SoftFwdParams p) {
   float a;
   if (p.phase == 1 && (int)blockIdx.z >= (p.plan + (size_t)blockIdx.y * p.plan_words)[2]) return;  // empty segment slice (CTA-uniform): before any other work
   if (!soft_uniform_applies(p, a)) return;
