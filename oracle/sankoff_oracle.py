@@ -292,3 +292,34 @@ def soft_sankoff_bwd(adj, cost, dp, n_all, n_leaves, T, g=1.0, dtype=np.float64)
         gbar[:, c, :] += contrib.sum(axis=1)
         reach[c] = True
   return gbar, dC
+
+
+def pointer_words(tables, n_states):
+  """The compact back-pointer form the CUDA library writes under a UNIFORM cost (include/trex_b200.h,
+  TREX_MODE_COMPACT_ARG), derived from the forward tables: per (site, internal node, child slot) a 32-bit word with
+  bits 0-4 = first minimum j of the child's dp row and bit 5+s = "the pointer of parent state s is s itself".
+  Returns uint32 (L, n_all, 2); rows of leaves stay 0.  ``decode_pointer_words`` inverts it; the round trip equals
+  ``tables['argmin']`` exactly when every pointer is s or j — the property the format rests on."""
+  dp, arg, kids = tables["dp"], tables["argmin"], tables["children"]
+  L, n_all, _ = dp.shape
+  assert n_states <= 27
+  words = np.zeros((L, n_all, 2), dtype=np.uint32)
+  s = np.arange(n_states)
+  for node in range(n_all):
+    for k in range(2):
+      c = int(kids[node, k])
+      if kids[node, 0] == -1 and kids[node, 1] == -1:
+        continue  # a leaf row of the table
+      # a missing child (-1) reads the LAST row as the reference's indexing does; the root is filled last, so that row
+      # was still all 1e5 when this node was computed: first minimum 0
+      j = dp[:, c, :].argmin(axis=1).astype(np.uint32) if c >= 0 else np.zeros(L, dtype=np.uint32)
+      stay = (arg[:, node, k, :] == s[None, :]).astype(np.uint32)
+      words[:, node, k] = j | (stay << (5 + s)[None, :].astype(np.uint32)).sum(axis=1, dtype=np.uint32)
+  return words
+
+
+def decode_pointer_words(words, n_states):
+  """(L, n_all, 2) uint32 -> (L, n_all, 2, A) int32 pointers: bit 5+s ? s : bits 0-4."""
+  s = np.arange(n_states, dtype=np.uint32)
+  w = words[..., None]
+  return np.where((w >> (5 + s)) & 1, s, w & 31).astype(np.int32)

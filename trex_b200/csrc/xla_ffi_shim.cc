@@ -96,10 +96,14 @@ ffi::Error RunSankoffImpl(cudaStream_t stream, ffi::ScratchAllocator scratch,
     if (Ba == 1 && nb > 1) return ffi::Error::InvalidArgument("trex run_sankoff: batch without a batched adjacency");
     TREX_TRY(trex_sankoff_plan_for_sites(adj_b, n_all, n_leaves, (int)nb, /*zero_root_selfloop=*/1, L, plan, stream));
     TREX_TRY(trex_encode_leaf_states(seq_b, n_leaves, L, L, A, leaf, stride, stream));
+    // run_sankoff returns the reconstruction, not the backtracking table: let the library write pointer words when the
+    // (traced) cost matrix turns out uniform; the traceback is given the same matrix and mode and reads either form
+    const int mode = TREX_MODE_AUTO | TREX_MODE_COMPACT_ARG;
     TREX_TRY(trex_sankoff_hard_fwd(plan, n_all, n_leaves, A, L, stride, (int)nb, leaf, cost_b, dp, arg, nullptr,
-                                   tot64 + b0, TREX_MODE_AUTO, stream));
+                                   tot64 + b0, mode, stream));
     if (return_path)
-      TREX_TRY(trex_sankoff_traceback(plan, n_all, n_leaves, A, L, stride, (int)nb, leaf, dp, arg, anc, nullptr, stream));
+      TREX_TRY(trex_sankoff_traceback_cost(plan, n_all, n_leaves, A, L, stride, (int)nb, leaf, cost_b, mode, dp, arg, anc,
+                                           nullptr, stream));
     for (int64_t t = 0; t < nb; ++t) {  // exports are per tree
       TREX_TRY(trex_sankoff_export_recon(n_all, n_leaves, L, stride, seq_b, L, leaf,
                                          anc ? anc + (size_t)t * n_int * stride : nullptr,
