@@ -15,7 +15,10 @@
  *  - Return value: 0 = ok, non-zero = error; `trex_last_error()` returns a thread-local message.
  *  - Native table layout is site-contiguous  [tree][node][state][site]  with row pitch
  *    `site_stride` (elements, multiple of 16, >= n_sites).  Pad lanes are written with
- *    unspecified values and are excluded from every reduction.
+ *    unspecified values and are excluded from every reduction.  The kernels move up to four sites per
+ *    lane with 8- and 16-byte accesses: every table pointer (dp, argmin, leaf/ancestral states, gradients)
+ *    must be 16-byte aligned — true of cudaMalloc / framework allocations and of any offset by whole trees or by
+ *    site blocks that start at a multiple of 64 sites.
  *  - Leaf states are uint8 codes: 0..A-1 observed state, >= A "no state" (the reference's
  *    dropped out-of-bounds scatter, sankoff.py:50: the leaf row stays all-1e5).
  *  - Internal node k (0-based) is node id n_leaves + k.  n_int = n_all - n_leaves.
