@@ -808,11 +808,15 @@ static int launch_gemm(const float* seqs, const TcBuffers& w, const GemmParams& 
 // One-kernel mode (the c2 shape 127 x 1000 x 4): small calls are bound by launches and by the split-K
 // atomics, not by the tensor pipe.  When the whole grid fits the SMs at once (1 CTA per SM), the dS units build Msym
 // themselves, every gram unit stores its partial tile to a slot of its own, and the gram units finish <M, G> and dAdj
-// behind tagged flags — no prep / final launches, no red.global.add, no zeroing.  TREX_TREE_COST_ONE=0 keeps the
-// three-kernel chain (tests compare the two).
+// behind tagged flags — no prep / final launches, no red.global.add, no zeroing.
+// OPT-IN (TREX_TREE_COST_ONE=1; tests compare it with the three-kernel chain): the flags make the CTAs of one grid
+// wait for each other, which is only safe while the whole grid is resident.  A grid that fits the SMs is, when it
+// runs alone — but two such calls on different streams could each hold part of the SMs and starve the other (the
+// waits give up after ~1 s and raise TcBuffers::err rather than hang).  A cooperative launch would rule that out;
+// it is not measured yet, and the gain at c2 is 4 % (15.7 vs 16.4 us), so the chain stays the default.
 static bool one_kernel_plan(int n_nodes, long long k, bool want_ds, GemmParams& gp) {
   const char* e = getenv("TREX_TREE_COST_ONE");
-  if (e && e[0] == '0') return false;
+  if (!e || e[0] != '1') return false;
   if (pad_nodes(n_nodes) != 128) return false;
   const int n_kb = (int)((k + 31) / 32);
   int kb_per = (n_kb + kOneMaxGram - 1) / kOneMaxGram;
