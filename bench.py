@@ -938,13 +938,21 @@ def run_gpu(args):
       line["weak_scaling"] = weak
     line.update(extras)
     if world == 1 and not args.no_extras:
+      def secondary(name, fn, *a):
+        # a failing secondary leg must not take the headline line with it: record the error and go on
+        try:
+          line[name] = fn(*a)
+        except Exception as e:  # noqa: BLE001
+          line[name] = {"error": f"{type(e).__name__}: {e}"[:300]}
+          print(f"bench: secondary leg {name} failed: {e!r}", file=sys.stderr, flush=True)
+
       if L == N_SITES:
-        line["general_cost"] = general_cost_bench(torch, leg.eng, peak)
-      line["generators"] = generators_bench(torch)
-      line["tree_cost"] = tree_cost_bench(torch)
-      line["fit_loop"] = fit_loop_bench(torch)
-      line["landscape_loss"] = landscape_bench(torch)
-      line["cpu_baseline"] = cpu_baseline(args.cpu_sites)
+        secondary("general_cost", general_cost_bench, torch, leg.eng, peak)
+      secondary("generators", generators_bench, torch)
+      secondary("tree_cost", tree_cost_bench, torch)
+      secondary("fit_loop", fit_loop_bench, torch)
+      secondary("landscape_loss", landscape_bench, torch)
+      secondary("cpu_baseline", cpu_baseline, args.cpu_sites)
     emit(line)
   if world > 1:
     dist.barrier()
